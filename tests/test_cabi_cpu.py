@@ -1,0 +1,108 @@
+"""CPU-only checks of the product's host side: the C-ABI library loads and exports every symbol
+include/b200vqe.h declares, the front end (FermionCompiler text, JW/BK, packing, UCCSD) is bit-exact
+against the oracle, and device entry points fail loudly without a GPU (no CPU fallback)."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+import pauli_oracle as po
+import xaccvqe_b200 as xb
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "b200vqe.h")).read()
+    names = sorted(set(re.findall(r"\b(b200vqe_[a-z0-9_]+)\s*\(", hdr)))
+    assert len(names) >= 35
+    lib = xb.capi.lib()
+    missing = [n for n in names if not hasattr(lib, n)]
+    assert not missing, missing
+
+
+def _has_gpu():
+    try:
+        import torch
+        return torch.cuda.is_available()
+    except Exception:
+        return False
+
+
+@pytest.mark.skipif(_has_gpu(), reason="only meaningful without a GPU")
+def test_no_cpu_fallback():
+    with pytest.raises(xb.B200Error) as ei:
+        xb.Backend(4)
+    assert "no CPU fallback" in str(ei.value) or "CUDA" in str(ei.value)
+
+
+@pytest.mark.parametrize("tr", ["jw", "bk"])
+def test_front_end_packing_bit_exact(golden, tr):
+    for key in ("h2_source", "rdm_h2_source", "jw_easy_source"):
+        op = xb.OpHandle.from_fermion_source(golden[key], tr)
+        xm, zm, cf = op.pack()
+        oop, n = po.compile_fermion_source(golden[key], tr)
+        oxm, ozm, ocf, oids = po.pack_terms(oop)
+        assert op.n_qubits() == n
+        assert np.array_equal(xm, oxm) and np.array_equal(zm, ozm)
+        assert np.array_equal(cf, ocf)            # same arithmetic order -> identical doubles
+        assert op.term_ids() == oids
+
+
+def test_text_round_trip(golden):
+    for key in ("six_qubit_118", "four_qubit_100", "tapered_h2", "deuteron_h3"):
+        op = xb.OpHandle.from_string(golden[key])
+        oop = po.op_from_string(golden[key])
+        xm, zm, cf = op.pack()
+        oxm, ozm, ocf, _ = po.pack_terms(oop)
+        assert np.array_equal(xm, oxm) and np.array_equal(zm, ozm) and np.array_equal(cf, ocf)
+        again = xb.OpHandle.from_string(op.to_string())
+        assert np.array_equal(again.pack()[2], cf)
+        assert po.pack_terms(po.op_from_string(op.to_string()))[2].tolist() == ocf.tolist()
+
+
+def test_operator_algebra_matches_oracle(golden):
+    a = xb.OpHandle.from_string(golden["deuteron_h3"])
+    b = xb.OpHandle.from_string(golden["four_qubit_100"])
+    oa, ob = po.op_from_string(golden["deuteron_h3"]), po.op_from_string(golden["four_qubit_100"])
+    for got, want in ((a.mul(b), po.op_mul(oa, ob)), (a.add(b), po.op_add(oa, ob)), (b.mul(b), po.op_mul(ob, ob)),
+                      (a.scale(0.5 - 2j), po.op_scale(oa, 0.5 - 2j))):
+        xm, zm, cf = got.pack()
+        oxm, ozm, ocf, _ = po.pack_terms(want)
+        assert np.array_equal(xm, oxm) and np.array_equal(zm, ozm)
+        assert np.abs(cf - ocf).max() < 1e-12 * max(1.0, np.abs(ocf).max())
+
+
+@pytest.mark.parametrize("nq,ne,tr", [(4, 2, "jw"), (4, 2, "bk"), (6, 2, "jw"), (8, 4, "bk"), (12, 4, "jw"), (12, 4, "bk")])
+def test_uccsd_rotations_match_oracle(nq, ne, tr):
+    x, z, ic, pa, npar = xb.uccsd_rotations(nq, ne, tr)
+    rots, onp = po.uccsd_rotations(nq, ne, tr)
+    assert npar == onp and len(rots) == len(x)
+    assert [int(v) for v in x] == [r[0] for r in rots]
+    assert [int(v) for v in z] == [r[1] for r in rots]
+    assert ic.tolist() == [r[2] for r in rots]
+    assert pa.tolist() == [r[3] for r in rots]
+
+
+def test_uccsd_gate_list_matches_oracle():
+    th = np.array([0.1, -0.2])
+    g = xb.uccsd_gates(4, 2, th)
+    want = po.uccsd_gates(4, 2, th)
+    inv = {v: k for k, v in xb.capi.GATE_ID.items()}
+    got = [(inv[x.gate], (x.q0, x.q1) if x.gate == 7 else (x.q0,), x.theta) for x in g]
+    assert len(got) == len(want)
+    for a, b in zip(got, want):
+        assert a[0] == b[0] and tuple(a[1]) == tuple(b[1]) and a[2] == b[2]
+
+
+def test_parse_errors():
+    with pytest.raises(xb.B200Error):
+        xb.OpHandle.from_string("(1,0) Q0")
+    with pytest.raises(xb.B200Error):
+        xb.OpHandle.from_fermion_source("__qpu__ k() {\nabc 0 1\n}", "jw")
+    with pytest.raises(xb.B200Error):
+        xb.OpHandle.from_fermion_source("__qpu__ k() {\n1.0 0 1 0 0\n}", "nope")
+    with pytest.raises(xb.B200Error):
+        xb.uccsd_rotations(2, 2, "jw")

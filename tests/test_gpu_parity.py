@@ -1,0 +1,232 @@
+"""GPU parity: the CUDA path, called through the C ABI (libb200vqe.so via ctypes), against the CPU
+oracle on the same inputs.  Tolerance: 1e-10 relative for energies / eigenvalues (BASELINE.json
+north_star), 1e-12 absolute per amplitude for states of unit norm; masks are bit-exact."""
+import numpy as np
+import pytest
+
+import c_oracle as co
+import pauli_oracle as po
+
+pytestmark = pytest.mark.gpu
+
+REL = 1e-10
+
+
+@pytest.fixture(scope="module")
+def xb():
+    import xaccvqe_b200
+    return xaccvqe_b200
+
+
+def rel(a, b):
+    return abs(a - b) / max(1.0, abs(b))
+
+
+def random_hamiltonian(n, T, seed, hermitian=True):
+    rng = np.random.default_rng(seed)
+    pa = rng.integers(0, 4, size=(T, n))          # 0 I, 1 X, 2 Y, 3 Z per qubit
+    pa[np.all(pa == 0, axis=1), 0] = 3
+    xm = np.zeros(T, np.uint64)
+    zm = np.zeros(T, np.uint64)
+    for q in range(n):
+        xm |= ((pa[:, q] == 1) | (pa[:, q] == 2)).astype(np.uint64) << np.uint64(q)
+        zm |= ((pa[:, q] == 3) | (pa[:, q] == 2)).astype(np.uint64) << np.uint64(q)
+    key = xm.astype(object) * (1 << 64) + zm.astype(object)
+    _, first = np.unique(np.array([int(k) for k in key], dtype=object), return_index=True)
+    xm, zm = xm[np.sort(first)], zm[np.sort(first)]
+    ny = np.array([bin(int(x) & int(z)).count("1") for x, z in zip(xm, zm)])
+    c = rng.normal(size=len(xm)).astype(np.complex128)
+    if not hermitian:
+        c = c + 1j * rng.normal(size=len(xm))
+    return xm, zm, c * (1j ** (ny % 4))
+
+
+def random_state(n, seed):
+    rng = np.random.default_rng(seed)
+    psi = rng.normal(size=1 << n) + 1j * rng.normal(size=1 << n)
+    return psi / np.linalg.norm(psi)
+
+
+def test_h2_ground_state_and_uccsd_energy(xb, golden):
+    """Config 1: H2 STO-3G 4 qubits, Lanczos ground state + UCCSD energy vs the reference goldens."""
+    op = xb.OpHandle.from_fermion_source(golden["h2_source"], "jw")
+    xm, zm, cf = op.pack()
+    oop, n = po.compile_fermion_source(golden["h2_source"])
+    oxm, ozm, ocf, _ = po.pack_terms(oop)
+    assert np.array_equal(xm, oxm) and np.array_equal(zm, ozm) and np.array_equal(cf, ocf)   # bit-exact packing
+    be = xb.Backend(4)
+    be.set_hamiltonian(xm, zm, cf)
+    e0, it, res = be.lanczos_ground(tol=1e-12, max_iter=64, want_vector=True, seed=7)
+    assert rel(e0, golden["h2_ground_energy_exact"]) < REL
+    vec = be.download(0, order=xb.capi.ORDER_REFERENCE)
+    e_ref, v_ref = po.diagonalize_reference(oop, 4)
+    assert abs(abs(np.vdot(v_ref, vec)) - 1.0) < 1e-9          # same eigenvector up to a phase, reference index order
+    # UCCSD energy at the reference's test point
+    x, z, ic, pa, npar = xb.uccsd_rotations(4, 2, "jw")
+    th = np.array(golden["h2_uccsd_params"])
+    be.reset(0, 0b0011)
+    be.apply_pauli_rotations(x, z, ic * th[pa])
+    e = be.expectation().real
+    assert abs(e - golden["h2_uccsd_energy_near"][0]) < golden["h2_uccsd_energy_near"][1]
+    assert rel(e, po.uccsd_energy(oop, 4, 2, th)) < REL
+    # the literal gate list gives the same state
+    psi_rot = be.download(0)
+    be.reset(0, 0)
+    be.apply_gates(xb.uccsd_gates(4, 2, th))
+    psi_gate = be.download(0)
+    assert abs(abs(np.vdot(psi_rot, psi_gate)) - 1.0) < 1e-12
+    assert np.abs(psi_gate - po.run_circuit(4, po.uccsd_gates(4, 2, th))).max() < 1e-12
+
+
+@pytest.mark.parametrize("n,T,seed", [(3, 7, 11), (8, 40, 12), (11, 60, 13), (16, 50, 14), (21, 24, 15), (22, 12, 16)])
+def test_expectation_and_apply_random(xb, n, T, seed):
+    xm, zm, cf = random_hamiltonian(n, T, seed)
+    psi = random_state(n, seed + 100)
+    be = xb.Backend(n)
+    be.n_slots(2)
+    be.set_hamiltonian(xm, zm, cf)
+    be.upload(psi)
+    e, per = be.expectation(per_term=True)
+    eo, pero = co.expect(n, xm, zm, cf, psi)
+    scale = np.abs(cf).sum()
+    assert abs(e - eo) < REL * scale
+    assert np.abs(per - pero.real).max() < 1e-11
+    alpha = be.apply_h(0, 1)
+    out = be.download(1)
+    ref = co.apply(n, xm, zm, cf, psi)
+    assert np.abs(out - ref).max() < 1e-12 * scale
+    assert abs(alpha - np.vdot(psi, ref)) < REL * scale
+
+
+def test_complex_coefficients(xb):
+    n = 10
+    xm, zm, cf = random_hamiltonian(n, 30, 5, hermitian=False)
+    psi = random_state(n, 6)
+    be = xb.Backend(n)
+    be.n_slots(2)
+    be.set_hamiltonian(xm, zm, cf)
+    be.upload(psi)
+    e = be.expectation()
+    eo, _ = co.expect(n, xm, zm, cf, psi)
+    assert abs(e - eo) < REL * np.abs(cf).sum()
+    be.apply_h(0, 1, want_alpha=False)
+    assert np.abs(be.download(1) - co.apply(n, xm, zm, cf, psi)).max() < 1e-12 * np.abs(cf).sum()
+
+
+def test_identity_and_diagonal_only(xb):
+    n = 9
+    xm = np.array([0, 0, 0, 0], np.uint64)
+    zm = np.array([0, 1, 0b101, 0b100000000], np.uint64)
+    cf = np.array([2.5, -1.0, 0.25, 3.0], complex)
+    psi = random_state(n, 3)
+    be = xb.Backend(n)
+    be.n_slots(2)
+    be.set_hamiltonian(xm, zm, cf)
+    be.upload(psi)
+    e, per = be.expectation(per_term=True)
+    eo, pero = co.expect(n, xm, zm, cf, psi)
+    assert abs(e - eo) < 1e-12 and per[0] == 1.0 and np.abs(per[1:] - pero.real[1:]).max() < 1e-12
+    be.apply_h(0, 1, want_alpha=False)
+    assert np.abs(be.download(1) - co.apply(n, xm, zm, cf, psi)).max() < 1e-12
+
+
+@pytest.mark.parametrize("n", [2, 5, 12, 21])
+def test_gates_and_rotations(xb, n):
+    rng = np.random.default_rng(n)
+    psi = random_state(n, 40 + n)
+    be = xb.Backend(n)
+    be.upload(psi)
+    gates = []
+    for _ in range(24):
+        name = ["X", "Y", "Z", "H", "Rx", "Ry", "Rz", "CNOT"][rng.integers(0, 8)]
+        if name == "CNOT":
+            a, b = rng.choice(n, 2, replace=False)
+            gates.append((name, (int(a), int(b)), 0.0))
+        else:
+            gates.append((name, (int(rng.integers(0, n)),), float(rng.normal())))
+    be.apply_gates(gates)
+    ref = psi.copy()
+    for name, qs, th in gates:
+        co.apply_gate(n, name, qs, th, ref)
+    assert np.abs(be.download() - ref).max() < 1e-12
+    xm, zm, _ = random_hamiltonian(n, 12, 77 + n)
+    xm[0] = 0                                    # a diagonal rotation too
+    phi = rng.normal(size=len(xm))
+    be.apply_pauli_rotations(xm, zm, phi)
+    for x, z, p in zip(xm, zm, phi):
+        co.pauli_rotation(n, int(x), int(z), float(p), ref)
+    assert np.abs(be.download() - ref).max() < 1e-12
+    assert abs(be.norm2() - 1.0) < 1e-12
+
+
+def test_product_state_expectation_exact(xb):
+    """<P> of a product state factorises: an oracle that needs no 2^n vector (used at full size in bench)."""
+    n = 20
+    rng = np.random.default_rng(9)
+    a, b = rng.uniform(0, np.pi, n), rng.uniform(0, 2 * np.pi, n)
+    xm, zm, cf = random_hamiltonian(n, 40, 21)
+    be = xb.Backend(n)
+    be.set_hamiltonian(xm, zm, cf)
+    be.product_state(a, b)
+    e, per = be.expectation(per_term=True)
+    # single-qubit expectations of cos a |0> + e^{ib} sin a |1>
+    ex, ey, ez = np.sin(2 * a) * np.cos(b), np.sin(2 * a) * np.sin(b), np.cos(2 * a)
+    want = np.ones(len(xm))
+    for k, (x, z) in enumerate(zip(xm, zm)):
+        for q in range(n):
+            xb_, zb_ = (int(x) >> q) & 1, (int(z) >> q) & 1
+            if xb_ and zb_:
+                want[k] *= ey[q]
+            elif xb_:
+                want[k] *= ex[q]
+            elif zb_:
+                want[k] *= ez[q]
+    assert np.abs(per - want).max() < 1e-11
+    ny = np.array([bin(int(x) & int(z)).count("1") for x, z in zip(xm, zm)])
+    c = (cf / (1j ** (ny % 4))).real
+    assert abs(e.real - np.dot(c, want)) < REL * np.abs(c).sum()
+
+
+@pytest.mark.parametrize("n,T,seed", [(6, 30, 1), (10, 80, 2), (14, 120, 3)])
+def test_lanczos_vs_dense(xb, n, T, seed):
+    xm, zm, cf = random_hamiltonian(n, T, seed)
+    be = xb.Backend(n)
+    be.set_hamiltonian(xm, zm, cf)
+    e0, it, res = be.lanczos_ground(tol=1e-11, max_iter=2000, want_vector=True, seed=seed)
+    if n <= 10:
+        A = np.zeros((1 << n, 1 << n), complex)
+        eye = np.eye(1 << n, dtype=complex)
+        for col in range(1 << n):
+            A[:, col] = co.apply(n, xm, zm, cf, eye[:, col])
+        w = np.linalg.eigvalsh(A)
+        want = w[0]
+    else:
+        want, _ = po.ground_state_eigsh(xm, zm, cf, n, tol=1e-13, apply=lambda v: co.apply(n, xm, zm, cf, v))
+    assert rel(e0, want) < REL
+    vec = be.download(0)
+    hv = co.apply(n, xm, zm, cf, vec)
+    assert np.linalg.norm(hv - e0 * vec) < 1e-7 * np.abs(cf).sum()
+
+
+def test_text_fixture_ground_states(xb, golden):
+    d = golden["derived"]
+    for key, want in (("six_qubit_118", d["six_qubit_E0"]), ("four_qubit_100", d["four_qubit_E0"]),
+                      ("deuteron_h2", d["deuteron_h2_E0"]), ("deuteron_h3", d["deuteron_h3_E0"])):
+        op = xb.OpHandle.from_string(golden[key])
+        xm, zm, cf = op.pack()
+        be = xb.Backend(op.n_qubits())
+        be.set_hamiltonian(xm, zm, cf)
+        e0, it, res = be.lanczos_ground(tol=1e-12, max_iter=200, seed=3)
+        assert rel(e0, want) < REL, key
+
+
+def test_errors_are_loud(xb):
+    be = xb.Backend(4)
+    with pytest.raises(xb.B200Error):
+        be.set_hamiltonian([1 << 5], [0], [1.0])          # outside the register
+    with pytest.raises(xb.B200Error):
+        be.upload(np.zeros(32, complex))
+    with pytest.raises(xb.B200Error):
+        be.apply_gates([("H", (9,), 0.0)])
+    with pytest.raises(xb.B200Error):
+        xb.OpHandle.from_string("(1,0) Q0")

@@ -1,0 +1,246 @@
+// Device backend behind the C ABI of include/b200vqe.h.  One context = one GPU (one shard).
+#include "../../include/b200vqe.h"
+#include "backend_ctx.hpp"
+#include "kernels_apply.cuh"
+#include "kernels_small.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <dlfcn.h>
+#include <numeric>
+
+using namespace b200vqe;
+
+// ------------------------------------------------------------------------------------------
+// NCCL through dlopen: the sharded path needs it, the single-GPU path must not depend on it.
+// ------------------------------------------------------------------------------------------
+namespace {
+struct NcclApi {
+    void *lib = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+    bool load(std::string &err) {
+        if (lib) return true;
+        const char *names[] = {"libnccl.so.2", "libnccl.so"};
+        for (const char *n : names) {
+            lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+            if (lib) break;
+        }
+        if (!lib) { err = std::string("cannot dlopen libnccl.so.2: ") + dlerror(); return false; }
+#define LOADSYM(field, name) \
+        field = reinterpret_cast<decltype(field)>(dlsym(lib, name)); \
+        if (!field) { err = std::string("libnccl lacks ") + name; lib = nullptr; return false; }
+        LOADSYM(GetUniqueId, "ncclGetUniqueId")
+        LOADSYM(CommInitRank, "ncclCommInitRank")
+        LOADSYM(CommDestroy, "ncclCommDestroy")
+        LOADSYM(AllGather, "ncclAllGather")
+        LOADSYM(AllReduce, "ncclAllReduce")
+        LOADSYM(Send, "ncclSend")
+        LOADSYM(Recv, "ncclRecv")
+        LOADSYM(GroupStart, "ncclGroupStart")
+        LOADSYM(GroupEnd, "ncclGroupEnd")
+        LOADSYM(GetErrorString, "ncclGetErrorString")
+#undef LOADSYM
+        return true;
+    }
+};
+NcclApi g_nccl;
+thread_local std::string g_err;
+}  // namespace
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) {                                                                   \
+            h->err = std::string(#call) + ": " + cudaGetErrorString(e_);                           \
+            return e_ == cudaErrorMemoryAllocation ? B200VQE_ENOMEM : B200VQE_ECUDA;               \
+        }                                                                                          \
+    } while (0)
+#define NK(call)                                                                                   \
+    do {                                                                                           \
+        ncclResult_t r_ = (call);                                                                  \
+        if (r_ != ncclSuccess) {                                                                   \
+            h->err = std::string(#call) + ": " + g_nccl.GetErrorString(r_);                        \
+            return B200VQE_ECOMM;                                                                  \
+        }                                                                                          \
+    } while (0)
+#define FAIL(code, msg) do { h->err = (msg); return (code); } while (0)
+#define LAUNCHED(h) do { ++(h)->launches; CK(cudaGetLastError()); } while (0)
+
+static int grid_for(const b200vqe_ctx *h, uint64_t work_items, int per_sm) {
+    const uint64_t cap = (uint64_t)h->n_sm * per_sm;
+    const uint64_t need = (work_items + kBlock - 1) / kBlock;
+    return (int)std::max<uint64_t>(1, std::min(cap, need));
+}
+
+static int ensure_slot(b200vqe_ctx *h, int slot) {
+    if (slot < 0 || slot >= (int)h->slots.size())
+        FAIL(B200VQE_EINVAL, "slot " + std::to_string(slot) + " out of range (call b200vqe_n_slots first; have " + std::to_string(h->slots.size()) + ")");
+    if (!h->slots[slot]) {
+        CK(cudaSetDevice(h->device));
+        CK(cudaMalloc(&h->slots[slot], h->nloc * sizeof(double2)));
+    }
+    return 0;
+}
+
+static int ensure_gather(b200vqe_ctx *h) {
+    if (h->world == 1 || h->gather) return 0;
+    CK(cudaMalloc(&h->gather, (size_t)h->world * h->nloc * sizeof(double2)));
+    return 0;
+}
+
+// Make the slab table for reading `src`: unsharded -> the slot itself; sharded -> all-gather the
+// shards into the staging buffer once (each peer shard crosses NVLink once per H application,
+// independent of the number of terms), then every group reads HBM-resident slabs.
+static int make_slabs(b200vqe_ctx *h, const double2 *src, Slabs &s) {
+    for (int i = 0; i < kMaxWorld; ++i) s.p[i] = nullptr;
+    if (h->world == 1) { s.p[0] = src; return 0; }
+    int rc = ensure_gather(h);
+    if (rc) return rc;
+    NK(g_nccl.AllGather(src, h->gather, h->nloc * 2, ncclDouble, h->comm, h->stream));
+    for (int t = 0; t < h->world; ++t) s.p[t] = h->gather + (size_t)t * h->nloc;
+    s.p[h->rank] = src;
+    return 0;
+}
+
+static int allreduce_doubles(b200vqe_ctx *h, double *dptr, size_t count) {
+    if (h->world == 1) return 0;
+    NK(g_nccl.AllReduce(dptr, dptr, count, ncclDouble, ncclSum, h->comm, h->stream));
+    return 0;
+}
+
+extern "C" {
+
+const char *b200vqe_global_error(void) { return g_err.c_str(); }
+
+int b200vqe_comm_unique_id(char id[128]) {
+    if (!g_nccl.load(g_err)) return B200VQE_ECOMM;
+    ncclUniqueId u;
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
+    ncclResult_t r = g_nccl.GetUniqueId(&u);
+    if (r != ncclSuccess) { g_err = g_nccl.GetErrorString(r); return B200VQE_ECOMM; }
+    memcpy(id, &u, 128);
+    return 0;
+}
+
+static int create_common(int n_qubits, int device, int rank, int world, const char *id, b200vqe_handle *out) {
+    if (!out) { g_err = "out is NULL"; return B200VQE_EINVAL; }
+    *out = nullptr;
+    if (world < 1 || world > kMaxWorld || (world & (world - 1))) { g_err = "world must be 1, 2, 4 or 8"; return B200VQE_EINVAL; }
+    int wl = 0;
+    while ((1 << wl) < world) ++wl;
+    if (n_qubits < 1 || n_qubits > 40 || n_qubits - wl < 1) { g_err = "n_qubits must be in [1, 40] and exceed log2(world)"; return B200VQE_EINVAL; }
+    if (rank < 0 || rank >= world) { g_err = "rank out of range"; return B200VQE_EINVAL; }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        g_err = std::string("no CUDA device available (") + cudaGetErrorString(e) + "); this backend has no CPU fallback";
+        return B200VQE_ECUDA;
+    }
+    if (device < 0 || device >= ndev) { g_err = "device index out of range"; return B200VQE_EINVAL; }
+    auto *h = new b200vqe_ctx();
+    h->n = n_qubits; h->nl = n_qubits - wl; h->nloc = 1ull << h->nl;
+    h->device = device; h->rank = rank; h->world = world;
+    h->slots.assign(1, nullptr);
+    auto fail = [&](const std::string &m, int code) { g_err = m; delete h; return code; };
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return fail(cudaGetErrorString(e), B200VQE_ECUDA);
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return fail(cudaGetErrorString(e), B200VQE_ECUDA);
+    h->n_sm = prop.multiProcessorCount;
+    h->smem_optin = (int)prop.sharedMemPerBlockOptin;
+    if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail(cudaGetErrorString(e), B200VQE_ECUDA);
+    cudaEventCreate(&h->ev0);
+    cudaEventCreate(&h->ev1);
+    if ((e = cudaMalloc(&h->partials, sizeof(double) * 16 * 4096)) != cudaSuccess) return fail(cudaGetErrorString(e), B200VQE_ENOMEM);
+    if ((e = cudaMalloc(&h->counter, sizeof(unsigned))) != cudaSuccess) return fail(cudaGetErrorString(e), B200VQE_ENOMEM);
+    cudaMemset(h->counter, 0, sizeof(unsigned));
+    if ((e = cudaMalloc(&h->d_out, sizeof(double) * kOutDoubles)) != cudaSuccess) return fail(cudaGetErrorString(e), B200VQE_ENOMEM);
+    if ((e = cudaMallocHost(&h->h_out, sizeof(double) * kOutDoubles)) != cudaSuccess) return fail(cudaGetErrorString(e), B200VQE_ENOMEM);
+    if (world > 1) {
+        if (!g_nccl.load(g_err)) { delete h; return B200VQE_ECOMM; }
+        ncclUniqueId u;
+        memcpy(&u, id, 128);
+        ncclResult_t r = g_nccl.CommInitRank(&h->comm, world, u, rank);
+        if (r != ncclSuccess) return fail(std::string("ncclCommInitRank: ") + g_nccl.GetErrorString(r), B200VQE_ECOMM);
+    }
+    *out = h;
+    return 0;
+}
+
+int b200vqe_create(int n_qubits, int device, b200vqe_handle *out) {
+    return create_common(n_qubits, device, 0, 1, nullptr, out);
+}
+int b200vqe_create_sharded(int n_qubits, int device, int rank, int world, const char id[128], b200vqe_handle *out) {
+    if (world > 1 && !id) { g_err = "id is NULL"; return B200VQE_EINVAL; }
+    return create_common(n_qubits, device, rank, world, id, out);
+}
+
+int b200vqe_destroy(b200vqe_handle h) {
+    if (!h) return 0;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    for (auto p : h->slots) if (p) cudaFree(p);
+    if (h->gather) cudaFree(h->gather);
+    h->ham.free_device();
+    cudaFree(h->partials); cudaFree(h->counter); cudaFree(h->d_out); cudaFreeHost(h->h_out);
+    if (h->d_alpha) cudaFree(h->d_alpha);
+    if (h->d_norm) cudaFree(h->d_norm);
+    if (h->d_ritz) cudaFree(h->d_ritz);
+    if (h->comm) g_nccl.CommDestroy(h->comm);
+    cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
+    cudaStreamDestroy(h->stream);
+    delete h;
+    return 0;
+}
+
+const char *b200vqe_last_error(b200vqe_handle h) { return h ? h->err.c_str() : g_err.c_str(); }
+
+int b200vqe_n_slots(b200vqe_handle h, int n_slots) {
+    if (!h) return B200VQE_EINVAL;
+    if (n_slots < 1 || n_slots > 16) FAIL(B200VQE_EINVAL, "n_slots must be in [1, 16]");
+    CK(cudaSetDevice(h->device));
+    for (int s = n_slots; s < (int)h->slots.size(); ++s) if (h->slots[s]) { cudaFree(h->slots[s]); }
+    h->slots.resize(n_slots, nullptr);
+    return 0;
+}
+
+int b200vqe_local_amplitudes(b200vqe_handle h, uint64_t *count, uint64_t *first_index) {
+    if (!h) return B200VQE_EINVAL;
+    if (count) *count = h->nloc;
+    if (first_index) *first_index = (uint64_t)h->rank << h->nl;
+    return 0;
+}
+
+int b200vqe_synchronize(b200vqe_handle h) {
+    if (!h) return B200VQE_EINVAL;
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+int b200vqe_kernel_launches(b200vqe_handle h, int64_t *count) {
+    if (!h || !count) return B200VQE_EINVAL;
+    *count = h->launches;
+    return 0;
+}
+int b200vqe_last_kernel_ms(b200vqe_handle h, double *ms) {
+    if (!h || !ms) return B200VQE_EINVAL;
+    *ms = h->last_ms;
+    return 0;
+}
+
+}  // extern "C"
+
+#include "backend_ham.inc"
+#include "backend_state.inc"
+#include "backend_small.inc"
+#include "backend_lanczos.inc"

@@ -1,0 +1,64 @@
+// Context of one device backend instance (one GPU / one shard).
+#pragma once
+#include <cuda_runtime.h>
+#include <nccl.h>
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "kernels.cuh"
+
+namespace b200vqe {
+
+constexpr int kOutDoubles = 256;   // device/host scalar scratch (bucket energies, norms, ...)
+
+struct Bucket { int h; int g_begin; int g_end; };   // h = -1: all-j form (weight 1), else pair form (weight 2)
+
+// Device tables of one Hamiltonian.  Two layouts of the same terms:
+//   expect: identity stripped, groups ordered by bucket, u_k = coef (even nY) | i*coef (odd nY)
+//   apply : identity kept,     groups ordered by xmask,  v_k = coef
+struct DeviceHam {
+    int64_t n_terms = 0;            // as given by the caller
+    int64_t n_terms_nonid = 0;
+    bool realc = true;
+    double ident_re = 0.0, ident_im = 0.0;
+    std::vector<int64_t> ident_idx; // caller indices of identity terms
+    int tile_R = 1;                 // R the tables were bucketed for
+
+    // expectation
+    std::vector<Bucket> buckets;
+    int n_groups_e = 0;
+    GroupDesc *gd_e = nullptr; uint64_t *tz_e = nullptr; double2 *tu_e = nullptr;
+    // apply
+    int n_groups_a = 0;
+    GroupDesc *gd_a = nullptr; uint64_t *tz_a = nullptr; double2 *tv_a = nullptr;
+    // per-term path (host copies, sorted by xmask): caller index, masks, r_k
+    std::vector<int64_t> pt_idx; std::vector<uint64_t> pt_x, pt_z; std::vector<int> pt_ny;
+    // host copies for the small-n kernels / stats
+    std::vector<GroupDesc> h_gd_a; std::vector<uint64_t> h_tz_a; std::vector<double2> h_tv_a;
+
+    void free_device() {
+        cudaFree(gd_e); cudaFree(tz_e); cudaFree(tu_e); cudaFree(gd_a); cudaFree(tz_a); cudaFree(tv_a);
+        gd_e = gd_a = nullptr; tz_e = tz_a = nullptr; tu_e = tv_a = nullptr;
+    }
+};
+
+}  // namespace b200vqe
+
+struct b200vqe_ctx {
+    int n = 0, nl = 0, device = 0, rank = 0, world = 1, n_sm = 148, smem_optin = 0;
+    uint64_t nloc = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::vector<double2 *> slots;
+    double2 *gather = nullptr;          // [world][nloc] staging of the peers' shards
+    b200vqe::DeviceHam ham;
+    double *partials = nullptr; unsigned *counter = nullptr;
+    double *d_out = nullptr, *h_out = nullptr;
+    double *d_alpha = nullptr, *d_norm = nullptr, *d_ritz = nullptr; int lanczos_cap = 0;
+    ncclComm_t comm = nullptr;
+    std::string err;
+    int64_t launches = 0;
+    double last_ms = 0.0;
+};
