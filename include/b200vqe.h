@@ -148,6 +148,8 @@ int b200vqe_sweep_energies(b200vqe_handle h, uint64_t basis_index, int64_t n_rot
 int b200vqe_synchronize(b200vqe_handle h);
 int b200vqe_kernel_launches(b200vqe_handle h, int64_t *count);    /* kernels launched by this handle so far */
 int b200vqe_last_kernel_ms(b200vqe_handle h, double *ms);          /* CUDA-event time of the last expectation/apply */
+int b200vqe_timer_start(b200vqe_handle h);                         /* records a CUDA event on the handle's stream */
+int b200vqe_timer_stop(b200vqe_handle h, double *ms);              /* records, synchronises, returns elapsed ms */
 
 #ifdef __cplusplus
 }

@@ -324,6 +324,14 @@ class Backend:
         self._ck(lib().b200vqe_kernel_launches(self.h, C.byref(v)))
         return v.value
 
+    def timer_start(self):
+        self._ck(lib().b200vqe_timer_start(self.h))
+
+    def timer_stop(self) -> float:
+        v = C.c_double()
+        self._ck(lib().b200vqe_timer_stop(self.h, C.byref(v)))
+        return v.value
+
     def last_kernel_ms(self) -> float:
         v = C.c_double()
         self._ck(lib().b200vqe_last_kernel_ms(self.h, C.byref(v)))

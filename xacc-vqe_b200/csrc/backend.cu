@@ -161,6 +161,8 @@ static int create_common(int n_qubits, int device, int rank, int world, const ch
     if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail(cudaGetErrorString(e), B200VQE_ECUDA);
     cudaEventCreate(&h->ev0);
     cudaEventCreate(&h->ev1);
+    cudaEventCreate(&h->ev_t0);
+    cudaEventCreate(&h->ev_t1);
     if ((e = cudaMalloc(&h->partials, sizeof(double) * 16 * 4096)) != cudaSuccess) return fail(cudaGetErrorString(e), B200VQE_ENOMEM);
     if ((e = cudaMalloc(&h->counter, sizeof(unsigned))) != cudaSuccess) return fail(cudaGetErrorString(e), B200VQE_ENOMEM);
     cudaMemset(h->counter, 0, sizeof(unsigned));
@@ -197,7 +199,7 @@ int b200vqe_destroy(b200vqe_handle h) {
     if (h->d_norm) cudaFree(h->d_norm);
     if (h->d_ritz) cudaFree(h->d_ritz);
     if (h->comm) g_nccl.CommDestroy(h->comm);
-    cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
+    cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1); cudaEventDestroy(h->ev_t0); cudaEventDestroy(h->ev_t1);
     cudaStreamDestroy(h->stream);
     delete h;
     return 0;
@@ -235,6 +237,23 @@ int b200vqe_kernel_launches(b200vqe_handle h, int64_t *count) {
 int b200vqe_last_kernel_ms(b200vqe_handle h, double *ms) {
     if (!h || !ms) return B200VQE_EINVAL;
     *ms = h->last_ms;
+    return 0;
+}
+
+int b200vqe_timer_start(b200vqe_handle h) {
+    if (!h) return B200VQE_EINVAL;
+    CK(cudaSetDevice(h->device));
+    CK(cudaEventRecord(h->ev_t0, h->stream));
+    return 0;
+}
+int b200vqe_timer_stop(b200vqe_handle h, double *ms) {
+    if (!h || !ms) return B200VQE_EINVAL;
+    CK(cudaSetDevice(h->device));
+    CK(cudaEventRecord(h->ev_t1, h->stream));
+    CK(cudaEventSynchronize(h->ev_t1));
+    float f = 0.f;
+    CK(cudaEventElapsedTime(&f, h->ev_t0, h->ev_t1));
+    *ms = f;
     return 0;
 }
 

@@ -50,7 +50,7 @@ struct b200vqe_ctx {
     int n = 0, nl = 0, device = 0, rank = 0, world = 1, n_sm = 148, smem_optin = 0;
     uint64_t nloc = 0;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_t0 = nullptr, ev_t1 = nullptr;
     std::vector<double2 *> slots;
     double2 *gather = nullptr;          // [world][nloc] staging of the peers' shards
     b200vqe::DeviceHam ham;
