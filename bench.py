@@ -192,6 +192,8 @@ def run_gpu(args):
     N = 1 << n
 
     be = xb.Backend(n, device=local_rank, rank=rank, world=world, comm_id=comm_id)
+    be.set_option("expect-engine", args.engine)
+    be.set_option("tile-chunk-bits", args.chunk_bits)
     be.set_hamiltonian(xm, zm, cf)
     Tn, G = be.hamiltonian_stats()
 
@@ -319,6 +321,8 @@ def main():
     ap.add_argument("--terms", type=int, default=N_TERMS)
     ap.add_argument("--cpu-terms", type=int, default=24, help="terms in the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--engine", default="auto", choices=["auto", "tile", "stream"], help="<psi|H|psi> kernel family")
+    ap.add_argument("--chunk-bits", type=int, default=3, help="tile engine: log2 contiguous amplitudes per HBM chunk")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

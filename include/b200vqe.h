@@ -89,6 +89,11 @@ int b200vqe_create_sharded(int n_qubits, int device, int rank, int world, const 
                            b200vqe_handle *out);
 int b200vqe_destroy(b200vqe_handle h);
 const char *b200vqe_last_error(b200vqe_handle h);
+/* String options in the manner of xacc::setOption(key, value) (e.g. task/tasks/DiagonalizeTask.cpp:15-30).
+ *   "expect-engine"   = "auto" | "tile" | "stream"   which <psi|H|psi> kernel set_hamiltonian prepares
+ *   "tile-chunk-bits" = "2".."8"                     contiguous amplitudes per HBM chunk of the tile engine
+ * Options take effect at the next b200vqe_set_hamiltonian. */
+int b200vqe_set_option(b200vqe_handle h, const char *key, const char *value);
 int b200vqe_n_slots(b200vqe_handle h, int n_slots);   /* number of resident statevectors (default 1) */
 int b200vqe_local_amplitudes(b200vqe_handle h, uint64_t *count, uint64_t *first_index);
 
@@ -98,6 +103,12 @@ int b200vqe_local_amplitudes(b200vqe_handle h, uint64_t *count, uint64_t *first_
 int b200vqe_set_hamiltonian(b200vqe_handle h, int64_t n_terms, const uint64_t *xmask,
                             const uint64_t *zmask, const double *coef_re, const double *coef_im);
 int b200vqe_hamiltonian_stats(b200vqe_handle h, int64_t *n_terms, int64_t *n_groups);
+
+/* Host-only view of the tile-engine plan (see csrc/tile_plan.hpp) for a Hermitian term list: raw
+ * TileBatch[128 B], TileGroup[16 B], TileTerm[16 B] records.  Call with NULL arrays for the counts. */
+int b200vqe_debug_tile_plan(int n_qubits, int chunk_bits, int64_t n_terms, const uint64_t *xmask, const uint64_t *zmask,
+                            const double *coef_re, const double *coef_im, int64_t *n_batches, int64_t *n_groups,
+                            int64_t *n_plan_terms, void *batches, void *groups, void *terms);
 
 /* State */
 int b200vqe_state_reset(b200vqe_handle h, int slot, uint64_t basis_index);

@@ -98,6 +98,26 @@ def test_expectation_and_apply_random(xb, n, T, seed):
     assert abs(alpha - np.vdot(psi, ref)) < REL * scale
 
 
+@pytest.mark.parametrize("n,T,seed,cbits", [(12, 30, 31, 3), (15, 200, 32, 2), (18, 64, 33, 3), (20, 48, 34, 5), (22, 20, 35, 8)])
+def test_tile_engine_matches_streaming_kernel_and_oracle(xb, n, T, seed, cbits):
+    """The two <psi|H|psi> kernel families (tile engine / streaming pair kernel) against the oracle."""
+    xm, zm, cf = random_hamiltonian(n, T, seed)
+    psi = random_state(n, seed + 100)
+    eo, _ = co.expect(n, xm, zm, cf, psi)
+    scale = np.abs(cf).sum()
+    got = {}
+    for engine in ("tile", "stream"):
+        be = xb.Backend(n)
+        be.set_option("expect-engine", engine)
+        be.set_option("tile-chunk-bits", cbits)
+        be.set_hamiltonian(xm, zm, cf)
+        be.upload(psi)
+        got[engine] = be.expectation()
+        assert abs(got[engine] - eo) < REL * scale, engine
+        be.close()
+    assert abs(got["tile"] - got["stream"]) < REL * scale
+
+
 def test_complex_coefficients(xb):
     n = 10
     xm, zm, cf = random_hamiltonian(n, 30, 5, hermitian=False)

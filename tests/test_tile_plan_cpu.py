@@ -1,0 +1,142 @@
+"""Host logic of the tile engine (csrc/tile_plan.hpp), checked on the CPU: the plan exported by
+b200vqe_debug_tile_plan is replayed in numpy with exactly the index arithmetic of k_tile_expect
+(coset representative, chunk combos, virtual masks, sign words, pair selection) and the resulting
+<psi|H|psi> must equal the C oracle's."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import c_oracle as co
+import xaccvqe_b200 as xb
+
+TILE_BITS = 12
+BATCH_DT = np.dtype([("basis", "<u8", 10), ("pivot", "u1", 10), ("pad0", "u1", 6), ("g_begin", "<i4"), ("g_end", "<i4"),
+                     ("pad1", "<i4", 6)])
+GROUP_DT = np.dtype([("kb", "<u4"), ("n_even", "<u4"), ("n_odd", "<u4"), ("xv", "<u2"), ("hsel", "<i2")])
+TERM_DT = np.dtype([("packed", "<u8"), ("u", "<f8")])
+
+
+def get_plan(n, c, xm, zm, cf):
+    lib = xb.capi.lib()
+    xm = np.ascontiguousarray(xm, np.uint64)
+    zm = np.ascontiguousarray(zm, np.uint64)
+    cr, ci = np.ascontiguousarray(cf.real), np.ascontiguousarray(cf.imag)
+    nb, ng, nt = C.c_int64(), C.c_int64(), C.c_int64()
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)
+    args = (C.c_int(n), C.c_int(c), C.c_int64(len(xm)), vp(xm), vp(zm), vp(cr), vp(ci), C.byref(nb), C.byref(ng), C.byref(nt))
+    assert lib.b200vqe_debug_tile_plan(*args, None, None, None) == 0
+    B, G, T = np.zeros(nb.value, BATCH_DT), np.zeros(ng.value, GROUP_DT), np.zeros(nt.value, TERM_DT)
+    assert BATCH_DT.itemsize == 128 and GROUP_DT.itemsize == 16 and TERM_DT.itemsize == 16
+    assert lib.b200vqe_debug_tile_plan(*args, vp(B), vp(G), vp(T)) == 0
+    return B, G, T
+
+
+def parity(a):
+    a = a.astype(np.uint64)
+    for s in (32, 16, 8, 4, 2, 1):
+        a = a ^ (a >> np.uint64(s))
+    return (a & np.uint64(1)).astype(np.int64)
+
+
+def replay(n, c, B, G, T, psi):
+    """What k_tile_expect computes, vectorised over (tile, thread, register)."""
+    M = TILE_BITS - c
+    n_tiles = 1 << (n - TILE_BITS)
+    v = np.arange(1 << TILE_BITS, dtype=np.uint64)          # virtual index: r<<8 | thread
+    mu = v >> np.uint64(c)
+    lo = v & np.uint64((1 << c) - 1)
+    total = 0.0
+    for b in B:
+        combo = np.zeros(1 << TILE_BITS, np.uint64)
+        for i in range(M):
+            combo ^= np.where((mu >> np.uint64(i)) & np.uint64(1), b["basis"][i], np.uint64(0)).astype(np.uint64)
+        for t in range(n_tiles):
+            rep = t
+            for i in range(M):
+                p = int(b["pivot"][i])
+                rep = ((rep >> p) << (p + 1)) | (rep & ((1 << p) - 1))
+            j = ((np.uint64(rep) ^ combo) << np.uint64(c)) | lo
+            tile = psi[j.astype(np.int64)]
+            for g in G[b["g_begin"]:b["g_end"]]:
+                xv, hs = int(g["xv"]), int(g["hsel"])
+                r = v >> np.uint64(8)
+                if hs >= 0:
+                    assert (xv >> (8 + hs)) & 1
+                    act = ((r >> np.uint64(hs)) & np.uint64(1)) == 0
+                else:
+                    assert (xv >> 8) == 0
+                    act = np.ones(len(v), bool)
+                va = v[act]
+                a, bb = tile[va.astype(np.int64)], tile[(va ^ np.uint64(xv)).astype(np.int64)]
+                w = np.conj(bb) * a
+                fe, go = np.zeros(len(va)), np.zeros(len(va))
+                k = int(g["kb"])
+                for which, cnt in ((0, int(g["n_even"])), (1, int(g["n_odd"]))):
+                    for _ in range(cnt):
+                        packed, u = int(T[k]["packed"]), float(T[k]["u"])
+                        p0 = (bin(rep & packed & ((1 << 40) - 1)).count("1") & 1) ^ parity(va & np.uint64(0xFF) & np.uint64((packed >> 40) & 0xFF))
+                        sw = (packed >> 48) & 0xFFFF
+                        sr = (np.uint64(sw) >> (va >> np.uint64(8))) & np.uint64(1)
+                        sign = 1.0 - 2.0 * (p0 ^ sr.astype(np.int64))
+                        if which == 0:
+                            fe += sign * u
+                        else:
+                            go += sign * u
+                        k += 1
+                total += float(np.sum(fe * w.real + go * w.imag))
+    return total
+
+
+def random_hamiltonian(n, T, seed, weights=None):
+    rng = np.random.default_rng(seed)
+    pa = rng.integers(0, 4, size=(T, n)) if weights is None else rng.choice(4, size=(T, n), p=weights)
+    pa[np.all(pa == 0, axis=1), 0] = 3
+    xm = np.zeros(T, np.uint64)
+    zm = np.zeros(T, np.uint64)
+    for q in range(n):
+        xm |= ((pa[:, q] == 1) | (pa[:, q] == 2)).astype(np.uint64) << np.uint64(q)
+        zm |= ((pa[:, q] == 3) | (pa[:, q] == 2)).astype(np.uint64) << np.uint64(q)
+    keys = {}
+    for k in range(T):
+        keys.setdefault((int(xm[k]), int(zm[k])), k)
+    idx = sorted(keys.values())
+    xm, zm = xm[idx], zm[idx]
+    ny = np.array([bin(int(x) & int(z)).count("1") for x, z in zip(xm, zm)])
+    return xm, zm, rng.normal(size=len(xm)) * (1j ** (ny % 4))
+
+
+@pytest.mark.parametrize("n,T,c,seed,weights", [
+    (12, 20, 3, 1, None), (13, 60, 3, 2, None), (14, 50, 2, 3, None), (14, 40, 5, 4, None), (15, 30, 8, 5, None),
+    (14, 120, 3, 6, (0.7, 0.1, 0.1, 0.1)),      # low-weight strings: many groups share a small subspace
+    (13, 80, 4, 7, (0.55, 0.0, 0.0, 0.45)),     # diagonal only
+])
+def test_plan_replay_matches_oracle(n, T, c, seed, weights):
+    xm, zm, cf = random_hamiltonian(n, T, seed, weights)
+    rng = np.random.default_rng(seed + 50)
+    psi = rng.normal(size=1 << n) + 1j * rng.normal(size=1 << n)
+    psi /= np.linalg.norm(psi)
+    B, G, Tt = get_plan(n, c, xm, zm, cf)
+    assert len(G) == len(set(int(x) for x in xm)) and len(Tt) == len(xm)
+    assert B["g_end"][-1] == len(G) and B["g_begin"][0] == 0
+    e = replay(n, c, B, G, Tt, psi)
+    eo, _ = co.expect(n, xm, zm, cf, psi)
+    assert abs(e - eo.real) < 1e-11 * np.abs(cf).sum()
+
+
+def test_plan_batches_many_groups_for_structured_masks():
+    """Flip masks spanning a small space (as JW molecular Hamiltonians do) collapse into few batches."""
+    n = 16
+    rng = np.random.default_rng(0)
+    gens = [int(g) for g in rng.integers(1, 1 << n, 7, dtype=np.uint64)]
+    xs = set()
+    for m in range(1, 1 << 7):
+        x = 0
+        for i in range(7):
+            if (m >> i) & 1:
+                x ^= gens[i]
+        xs.add(x)
+    xm = np.array(sorted(xs), np.uint64)
+    zm = np.zeros(len(xm), np.uint64)
+    B, G, _ = get_plan(n, 3, xm, zm, np.ones(len(xm), complex))
+    assert len(G) == len(xm) and len(B) <= 2

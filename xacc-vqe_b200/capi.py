@@ -226,6 +226,10 @@ class Backend:
         if rc:
             raise B200Error(rc, lib().b200vqe_last_error(self.h).decode())
 
+    def set_option(self, key: str, value):
+        """String options (xacc::setOption style); take effect at the next set_hamiltonian."""
+        self._ck(lib().b200vqe_set_option(self.h, key.encode(), str(value).encode()))
+
     def n_slots(self, n: int):
         self._ck(lib().b200vqe_n_slots(self.h, C.c_int(n)))
 

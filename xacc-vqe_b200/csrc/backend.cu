@@ -3,6 +3,7 @@
 #include "backend_ctx.hpp"
 #include "kernels_apply.cuh"
 #include "kernels_small.cuh"
+#include "kernels_tile.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -221,6 +222,27 @@ int b200vqe_local_amplitudes(b200vqe_handle h, uint64_t *count, uint64_t *first_
     if (count) *count = h->nloc;
     if (first_index) *first_index = (uint64_t)h->rank << h->nl;
     return 0;
+}
+
+// string options in the manner of xacc::setOption(key, value)
+int b200vqe_set_option(b200vqe_handle h, const char *key, const char *value) {
+    if (!h) return B200VQE_EINVAL;
+    if (!key || !value) FAIL(B200VQE_EINVAL, "null option key / value");
+    const std::string k(key), v(value);
+    if (k == "expect-engine") {
+        if (v == "auto") h->opt_expect_engine = 0;
+        else if (v == "tile") h->opt_expect_engine = 1;
+        else if (v == "stream") h->opt_expect_engine = 2;
+        else FAIL(B200VQE_EINVAL, "expect-engine must be auto, tile or stream");
+        return 0;
+    }
+    if (k == "tile-chunk-bits") {
+        const int c = atoi(value);
+        if (c < 2 || c > 8) FAIL(B200VQE_EINVAL, "tile-chunk-bits must be in [2, 8]");
+        h->opt_tile_chunk_bits = c;
+        return 0;
+    }
+    FAIL(B200VQE_EINVAL, "unknown option '" + k + "'");
 }
 
 int b200vqe_synchronize(b200vqe_handle h) {

@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "kernels.cuh"
+#include "tile_plan.hpp"
 
 namespace b200vqe {
 
@@ -35,12 +36,17 @@ struct DeviceHam {
     GroupDesc *gd_a = nullptr; uint64_t *tz_a = nullptr; double2 *tv_a = nullptr;
     // per-term path (host copies, sorted by xmask): caller index, masks, r_k
     std::vector<int64_t> pt_idx; std::vector<uint64_t> pt_x, pt_z; std::vector<int> pt_ny;
+    // tile engine (kernels_tile.cuh): batches of xmask groups evaluated per HBM read of the state
+    int tile_C = 0, tile_M = 0, n_tile_batches = 0, n_tile_groups = 0;
+    TileBatch *tl_batches = nullptr; TileGroup *tl_groups = nullptr; TileTerm *tl_terms = nullptr;
     // host copies for the small-n kernels / stats
     std::vector<GroupDesc> h_gd_a; std::vector<uint64_t> h_tz_a; std::vector<double2> h_tv_a;
 
     void free_device() {
         cudaFree(gd_e); cudaFree(tz_e); cudaFree(tu_e); cudaFree(gd_a); cudaFree(tz_a); cudaFree(tv_a);
+        cudaFree(tl_batches); cudaFree(tl_groups); cudaFree(tl_terms);
         gd_e = gd_a = nullptr; tz_e = tz_a = nullptr; tu_e = tv_a = nullptr;
+        tl_batches = nullptr; tl_groups = nullptr; tl_terms = nullptr;
     }
 };
 
@@ -61,4 +67,7 @@ struct b200vqe_ctx {
     std::string err;
     int64_t launches = 0;
     double last_ms = 0.0;
+    // options (string keys as in the reference's xacc::setOption map)
+    int opt_expect_engine = 0;          // 0 auto, 1 tile engine, 2 streaming kernel
+    int opt_tile_chunk_bits = 3;        // C: contiguous amplitudes per chunk = 2^C (128 B at C = 3)
 };

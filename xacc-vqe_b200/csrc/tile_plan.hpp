@@ -1,0 +1,229 @@
+// Host-side planner of the tile engine (kernels_tile.cuh).
+//
+// Idea.  <psi|P|psi> for a Pauli string with flip mask x pairs amplitude j with j^x.  A CTA that
+// holds in shared memory a set of amplitudes closed under j -> j^x for SEVERAL masks x_1..x_d can
+// evaluate all of those xmask groups from one HBM read of the set.  The closed sets are the cosets
+// of the GF(2) subspace S = span(x_1 >> C, ...) of the high index bits; each coset is 2^M chunks of
+// 2^C contiguous amplitudes (M = dim S, tile = 2^(M+C) amplitudes).  Inside a tile the amplitudes
+// form a "virtual register" of M+C qubits: chunk coordinate mu (bit i <-> basis vector i) and the
+// low C index bits; group x acts there as the virtual mask xv = (mu(x) << C) | (x & (2^C-1)), and
+// the Z parity splits into a per-coset part, parity(rep & z_hi), and a virtual part parity(v & zv)
+// with zv = (Zv << C) | (z & (2^C-1)),  Zv bit i = parity(basis_i & z_hi).
+//
+// The planner partitions the xmask groups of a Hamiltonian into batches, one subspace each, and
+// emits the device tables.  HBM traffic per group drops from 8 B (pair form of the streaming kernel)
+// to 16/d B per amplitude, d = groups per batch (>= M for unstructured Hamiltonians, far more for
+// molecular ones whose flip masks span a small space).
+#pragma once
+#include <algorithm>
+#include <cstdint>
+#include <unordered_map>
+#include <vector>
+
+namespace b200vqe {
+
+constexpr int kTileBits = 12;        // tile = 4096 amplitudes = 64 KB of double2
+constexpr int kTileRegBits = 4;      // 16 amplitudes per thread (virtual bits 8..11)
+constexpr int kTileMaxDim = 10;      // M = kTileBits - C, C >= 2
+
+struct TileBatch {                   // 128 bytes
+    uint64_t basis[kTileMaxDim];     // basis[i] <-> virtual bit C + i; acts on the high index (j >> C)
+    uint8_t pivot[kTileMaxDim];      // pivot positions in the high index, ascending (for coset reps)
+    uint8_t pad0[6];
+    int32_t g_begin, g_end;          // groups of this batch
+    int32_t pad1[6];
+};
+static_assert(sizeof(TileBatch) == 128, "TileBatch layout");
+
+struct TileGroup {                   // 16 bytes
+    uint32_t kb;                     // first term
+    uint32_t n_even;                 // terms with even nY (use Re w), then n_odd with odd nY (use Im w)
+    uint32_t n_odd;
+    uint16_t xv;                     // virtual flip mask (kTileBits bits)
+    int16_t hsel;                    // register bit (0..3) selecting one element per pair, -1: visit all
+};
+static_assert(sizeof(TileGroup) == 16, "TileGroup layout");
+
+struct TileTerm {                    // 16 bytes
+    uint64_t packed;                 // bits 0..39 z_hi | 40..47 zv & 0xff | 48..63 sign word over the 16 registers
+    double u;                        // weight * (coef | i*coef): real for a Hermitian H
+};
+static_assert(sizeof(TileTerm) == 16, "TileTerm layout");
+
+struct TilePlanTermIn { uint64_t x, z; double u; int odd; int64_t idx; };
+
+struct TilePlan {
+    int n = 0, C = 0, M = 0;
+    std::vector<TileBatch> batches;
+    std::vector<TileGroup> groups;
+    std::vector<TileTerm> terms;
+    std::vector<int64_t> term_src;   // plan term -> index into the input array
+};
+
+namespace tileplan {
+
+inline int parity64h(uint64_t v) { return __builtin_popcountll(v) & 1; }
+
+// reduced basis with unique pivots, pivot = highest set bit of each vector
+struct Rref {
+    std::vector<uint64_t> b;
+    std::vector<int> piv;
+    uint64_t reduce(uint64_t v) const {
+        for (size_t i = 0; i < b.size(); ++i) if ((v >> piv[i]) & 1) v ^= b[i];
+        return v;
+    }
+    bool insert(uint64_t v) {
+        v = reduce(v);
+        if (!v) return false;
+        const int p = 63 - __builtin_clzll(v);
+        for (size_t i = 0; i < b.size(); ++i) if ((b[i] >> p) & 1) b[i] ^= v;
+        b.push_back(v);
+        piv.push_back(p);
+        return true;
+    }
+    uint64_t coords(uint64_t v) const {   // valid when reduce(v) == 0
+        uint64_t mu = 0;
+        for (size_t i = 0; i < b.size(); ++i) mu |= ((v >> piv[i]) & 1ull) << i;
+        return mu;
+    }
+};
+
+inline uint16_t sign_word16(unsigned zr) {   // bit r = parity(r & zr), r = 0..15
+    uint16_t w = 0;
+    for (unsigned r = 0; r < 16; ++r) w |= (uint16_t)((__builtin_popcount(r & zr) & 1) << r);
+    return w;
+}
+
+}  // namespace tileplan
+
+// terms: non-identity terms with u already set (coef or i*coef, real part).  Groups of equal x.
+inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> &in) {
+    using namespace tileplan;
+    TilePlan P;
+    P.n = n; P.C = C; P.M = kTileBits - C;
+    const int M = P.M;
+    const int nh = n - C;                         // bits of the high index
+    const uint64_t lomask = (1ull << C) - 1;
+
+    // ---- groups by x (sorted) ----
+    std::vector<int64_t> order(in.size());
+    for (size_t i = 0; i < in.size(); ++i) order[i] = (int64_t)i;
+    std::stable_sort(order.begin(), order.end(), [&](int64_t a, int64_t b) {
+        if (in[a].x != in[b].x) return in[a].x < in[b].x;
+        if (in[a].odd != in[b].odd) return in[a].odd < in[b].odd;
+        return in[a].z < in[b].z;
+    });
+    struct G { uint64_t x; size_t tb, te; };
+    std::vector<G> gs;
+    for (size_t i = 0; i < order.size();) {
+        size_t j = i;
+        while (j < order.size() && in[order[j]].x == in[order[i]].x) ++j;
+        gs.push_back(G{in[order[i]].x, i, j});
+        i = j;
+    }
+    const size_t NG = gs.size();
+    std::unordered_map<uint64_t, std::vector<size_t>> by_hi;
+    by_hi.reserve(NG * 2);
+    for (size_t g = 0; g < NG; ++g) by_hi[gs[g].x >> C].push_back(g);
+    std::vector<char> done(NG, 0);
+    size_t n_done = 0, cursor = 0;
+
+    while (n_done < NG) {
+        while (done[cursor]) ++cursor;
+        // ---- choose the subspace: greedy over the next unassigned groups ----
+        Rref rr;
+        size_t scanned = 0;
+        for (size_t g = cursor; g < NG && (int)rr.b.size() < M && scanned < 8192; ++g) {
+            if (done[g]) continue;
+            ++scanned;
+            rr.insert(gs[g].x >> C);
+        }
+        for (int p = 0; p < nh && (int)rr.b.size() < M; ++p) rr.insert(1ull << p);   // pad with unit vectors
+        // ---- members: every unassigned group whose high mask lies in the span ----
+        std::vector<size_t> members;
+        const size_t remaining = NG - n_done;
+        if (remaining <= (1ull << rr.b.size())) {
+            for (size_t g = cursor; g < NG; ++g)
+                if (!done[g] && rr.reduce(gs[g].x >> C) == 0) members.push_back(g);
+        } else {
+            for (uint64_t m = 0; m < (1ull << rr.b.size()); ++m) {
+                uint64_t v = 0;
+                for (size_t i = 0; i < rr.b.size(); ++i) if ((m >> i) & 1) v ^= rr.b[i];
+                auto it = by_hi.find(v);
+                if (it == by_hi.end()) continue;
+                for (size_t g : it->second) if (!done[g]) members.push_back(g);
+            }
+            std::sort(members.begin(), members.end());
+        }
+        // ---- order the basis: the kTileRegBits coordinates that cover most work go on the register bits ----
+        const int dim = (int)rr.b.size();
+        std::vector<uint64_t> mu(members.size());
+        std::vector<double> cost(members.size());
+        for (size_t k = 0; k < members.size(); ++k) {
+            mu[k] = rr.coords(gs[members[k]].x >> C);
+            cost[k] = 4.0 + (double)(gs[members[k]].te - gs[members[k]].tb);
+        }
+        std::vector<int> perm;                     // perm[new position] = old index
+        std::vector<char> used(dim, 0), covered(members.size(), 0);
+        std::vector<int> top;
+        for (int pick = 0; pick < kTileRegBits && pick < dim; ++pick) {
+            int best = -1;
+            double bestw = -1.0;
+            for (int i = 0; i < dim; ++i) {
+                if (used[i]) continue;
+                double w = 0.0;
+                for (size_t k = 0; k < members.size(); ++k) if (!covered[k] && ((mu[k] >> i) & 1)) w += cost[k];
+                if (w > bestw) { bestw = w; best = i; }
+            }
+            used[best] = 1;
+            top.push_back(best);
+            for (size_t k = 0; k < members.size(); ++k) if ((mu[k] >> best) & 1) covered[k] = 1;
+        }
+        for (int i = 0; i < dim; ++i) if (!used[i]) perm.push_back(i);
+        for (int t : top) perm.push_back(t);       // register bits are the top kTileRegBits coordinates
+
+        TileBatch B{};
+        for (int i = 0; i < dim; ++i) B.basis[i] = rr.b[perm[i]];
+        std::vector<int> sp(rr.piv.begin(), rr.piv.end());
+        std::sort(sp.begin(), sp.end());
+        for (int i = 0; i < dim; ++i) B.pivot[i] = (uint8_t)sp[i];
+        B.g_begin = (int32_t)P.groups.size();
+        auto permute_mu = [&](uint64_t m) {
+            uint64_t r = 0;
+            for (int i = 0; i < dim; ++i) r |= ((m >> perm[i]) & 1ull) << i;
+            return r;
+        };
+        for (size_t k = 0; k < members.size(); ++k) {
+            const G &g = gs[members[k]];
+            const uint64_t m = permute_mu(mu[k]);
+            TileGroup tg{};
+            tg.xv = (uint16_t)((m << C) | (g.x & lomask));
+            const unsigned xr = tg.xv >> (kTileBits - kTileRegBits);
+            tg.hsel = xr ? (int16_t)(31 - __builtin_clz(xr)) : (int16_t)-1;
+            const double weight = tg.hsel >= 0 ? 2.0 : 1.0;
+            tg.kb = (uint32_t)P.terms.size();
+            for (size_t t = g.tb; t < g.te; ++t) {
+                const TilePlanTermIn &ti = in[order[t]];
+                const uint64_t zhi = ti.z >> C;
+                uint64_t Zv = 0;
+                for (int i = 0; i < dim; ++i) Zv |= (uint64_t)parity64h(B.basis[i] & zhi) << i;
+                const unsigned zv = (unsigned)((Zv << C) | (ti.z & lomask));
+                TileTerm tt;
+                tt.packed = (zhi & ((1ull << 40) - 1)) | ((uint64_t)(zv & 0xffu) << 40) |
+                            ((uint64_t)sign_word16(zv >> (kTileBits - kTileRegBits)) << 48);
+                tt.u = weight * ti.u;
+                P.terms.push_back(tt);
+                P.term_src.push_back(ti.idx);
+                ti.odd ? ++tg.n_odd : ++tg.n_even;
+            }
+            P.groups.push_back(tg);
+            done[members[k]] = 1;
+            ++n_done;
+        }
+        B.g_end = (int32_t)P.groups.size();
+        P.batches.push_back(B);
+    }
+    return P;
+}
+
+}  // namespace b200vqe
