@@ -194,6 +194,7 @@ def run_gpu(args):
     be = xb.Backend(n, device=local_rank, rank=rank, world=world, comm_id=comm_id)
     be.set_option("expect-engine", args.engine)
     be.set_option("tile-chunk-bits", args.chunk_bits)
+    be.set_option("tile-ctas-per-sm", args.tile_ctas)
     be.set_hamiltonian(xm, zm, cf)
     Tn, G = be.hamiltonian_stats()
 
@@ -322,6 +323,7 @@ def main():
     ap.add_argument("--cpu-terms", type=int, default=24, help="terms in the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--engine", default="auto", choices=["auto", "tile", "stream"], help="<psi|H|psi> kernel family")
+    ap.add_argument("--tile-ctas", type=int, default=2, choices=[2, 3], help="tile engine: resident CTAs per SM")
     ap.add_argument("--chunk-bits", type=int, default=3, help="tile engine: log2 contiguous amplitudes per HBM chunk")
     args = ap.parse_args()
     if args.impl == "reference":

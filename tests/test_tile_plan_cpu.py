@@ -11,8 +11,8 @@ import c_oracle as co
 import xaccvqe_b200 as xb
 
 TILE_BITS = 12
-BATCH_DT = np.dtype([("basis", "<u8", 10), ("pivot", "u1", 10), ("pad0", "u1", 6), ("g_begin", "<i4"), ("g_end", "<i4"),
-                     ("pad1", "<i4", 6)])
+BATCH_DT = np.dtype([("basis", "<u4", 10), ("pivot", "u1", 10), ("pad0", "u1", 2), ("g_begin", "<i4"), ("g_end", "<i4"),
+                     ("t_begin", "<i4"), ("t_end", "<i4"), ("cls_end", "<i4", 5), ("pad1", "<i4", 10)])
 GROUP_DT = np.dtype([("kb", "<u4"), ("n_even", "<u4"), ("n_odd", "<u4"), ("xv", "<u2"), ("hsel", "<i2")])
 TERM_DT = np.dtype([("packed", "<u8"), ("u", "<f8")])
 
@@ -50,7 +50,7 @@ def replay(n, c, B, G, T, psi):
     for b in B:
         combo = np.zeros(1 << TILE_BITS, np.uint64)
         for i in range(M):
-            combo ^= np.where((mu >> np.uint64(i)) & np.uint64(1), b["basis"][i], np.uint64(0)).astype(np.uint64)
+            combo ^= np.where((mu >> np.uint64(i)) & np.uint64(1), np.uint64(b["basis"][i]), np.uint64(0)).astype(np.uint64)
         for t in range(n_tiles):
             rep = t
             for i in range(M):
@@ -58,6 +58,10 @@ def replay(n, c, B, G, T, psi):
                 rep = ((rep >> p) << (p + 1)) | (rep & ((1 << p) - 1))
             j = ((np.uint64(rep) ^ combo) << np.uint64(c)) | lo
             tile = psi[j.astype(np.int64)]
+            cls = [int(g["hsel"]) for g in G[b["g_begin"]:b["g_end"]]]
+            want_cls = sum(([c] * (int(e) - (int(b["cls_end"][i - 1]) if i else 0)) for i, (c, e) in
+                            enumerate(zip((0, 1, 2, 3, -1), b["cls_end"]))), [])
+            assert cls == want_cls and int(b["cls_end"][4]) == len(cls)
             for g in G[b["g_begin"]:b["g_end"]]:
                 xv, hs = int(g["xv"]), int(g["hsel"])
                 r = v >> np.uint64(8)
@@ -75,10 +79,10 @@ def replay(n, c, B, G, T, psi):
                 for which, cnt in ((0, int(g["n_even"])), (1, int(g["n_odd"]))):
                     for _ in range(cnt):
                         packed, u = int(T[k]["packed"]), float(T[k]["u"])
-                        p0 = (bin(rep & packed & ((1 << 40) - 1)).count("1") & 1) ^ parity(va & np.uint64(0xFF) & np.uint64((packed >> 40) & 0xFF))
-                        sw = (packed >> 48) & 0xFFFF
-                        sr = (np.uint64(sw) >> (va >> np.uint64(8))) & np.uint64(1)
-                        sign = 1.0 - 2.0 * (p0 ^ sr.astype(np.int64))
+                        p0 = (bin(rep & packed & 0xFFFFFFFF).count("1") & 1) ^ parity(va & np.uint64(0xFF) & np.uint64((packed >> 32) & 0xFF))
+                        zr = (packed >> 40) & 0xF
+                        sr = parity((va >> np.uint64(8)) & np.uint64(zr))
+                        sign = 1.0 - 2.0 * (p0 ^ sr)
                         if which == 0:
                             fe += sign * u
                         else:

@@ -242,6 +242,12 @@ int b200vqe_set_option(b200vqe_handle h, const char *key, const char *value) {
         h->opt_tile_chunk_bits = c;
         return 0;
     }
+    if (k == "tile-ctas-per-sm") {
+        const int c = atoi(value);
+        if (c != 2 && c != 3) FAIL(B200VQE_EINVAL, "tile-ctas-per-sm must be 2 or 3");
+        h->opt_tile_ctas = c;
+        return 0;
+    }
     FAIL(B200VQE_EINVAL, "unknown option '" + k + "'");
 }
 

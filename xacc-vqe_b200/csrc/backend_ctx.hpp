@@ -69,5 +69,6 @@ struct b200vqe_ctx {
     double last_ms = 0.0;
     // options (string keys as in the reference's xacc::setOption map)
     int opt_expect_engine = 0;          // 0 auto, 1 tile engine, 2 streaming kernel
+    int opt_tile_ctas = 2;              // resident CTAs per SM of the tile engine (2 or 3)
     int opt_tile_chunk_bits = 3;        // C: contiguous amplitudes per chunk = 2^C (128 B at C = 3)
 };

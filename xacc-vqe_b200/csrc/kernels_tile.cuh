@@ -5,9 +5,10 @@
 // that are the "bit h clear" element of their pair {v, v^xv} (all 16 when the group has no register
 // bit), reads the partner from shared memory (one conflict-free LDS.128) and accumulates
 //     E += fe(j) Re w + go(j) Im w,   w = conj(psi[j^x]) psi[j],
-// fe/go being the signed coefficient sums of the group's even-/odd-nY terms at j.  Signs come from
-// one 64-bit POPC per term (coset part), one 8-bit POPC (thread part) and a host-made 16-bit sign
-// word over the register index, so the per-amplitude cost of a term is a shift, a LOP3 and a DADD.
+// fe/go being the signed coefficient sums of the group's even-/odd-nY terms at j.  The sign of a term
+// at register r factorises into a thread constant (one 64-bit POPC for the coset part, one 8-bit POPC
+// for the thread part) and a Walsh function of r, so a term costs one 8-point signed butterfly (7 DFMA)
+// per thread on top of the group's Re w / Im w products: about one DFMA per pair per term.
 //
 // HBM traffic: 16 B per amplitude per BATCH (>= kTileBits - C groups), no writes.
 #pragma once
@@ -24,68 +25,108 @@ __device__ __forceinline__ double flip_bit(double v, unsigned word, int r) {
 
 struct TileTermRaw { unsigned long long packed; double u; };
 
-__device__ __forceinline__ TileTermRaw load_term(const TileTerm *__restrict__ terms, uint32_t k) {
-    const double2 raw = __ldg(reinterpret_cast<const double2 *>(terms) + k);
+// descriptor tables are read through generic pointers: shared memory when the batch's tables were staged
+// there (the usual case), global memory otherwise
+__device__ __forceinline__ TileTermRaw load_term(const TileTerm *terms, uint32_t k) {
+    const double2 raw = *(reinterpret_cast<const double2 *>(terms) + k);
     TileTermRaw t;
     t.packed = (unsigned long long)__double_as_longlong(raw.x);
     t.u = raw.y;
     return t;
 }
 
-// visits the 8 registers r whose bit HS equals BV
-template <int HS, int BV>
-__device__ __forceinline__ void tile_group(const double2 (&a)[16], const double2 *__restrict__ tile, unsigned v0,
-                                           unsigned long long rep, const TileGroup g,
-                                           const TileTerm *__restrict__ terms, double (&acc)[4]) {
-    constexpr int NA = 8;
-    double fe[NA], go[NA];
+// Signed sum over the 8 visited registers:  sum_i (-1)^{parity(i & zi)} w[i]  as a 3-stage butterfly whose
+// stage signs are the +-1.0 doubles s0..s2 (one DFMA per node, 7 in total).
+__device__ __forceinline__ double signed_sum8(const double (&w)[8], double s0, double s1, double s2) {
+    const double y0 = fma(s0, w[1], w[0]), y1 = fma(s0, w[3], w[2]), y2 = fma(s0, w[5], w[4]), y3 = fma(s0, w[7], w[6]);
+    const double x0 = fma(s1, y1, y0), x1 = fma(s1, y3, y2);
+    return fma(s2, x1, x0);
+}
+
+__device__ __forceinline__ double pm_one_hi(unsigned hi_word, int bit) {   // bit of hi_word set ? -1.0 : 1.0
+    const unsigned m = bit == 31 ? hi_word : (hi_word << (31 - bit));
+    return __hiloint2double((int)((m & 0x80000000u) | 0x3ff00000u), 0);
+}
+
+// One xmask group on the 8 registers r whose bit HS equals BV (the other element of each pair has the
+// bit flipped when the group's xv has register bit HS; groups without a register bit call this for
+// BV = 0 and BV = 1).  WHICH = 0: even-nY terms on Re w, 1: odd-nY terms on Im w.
+template <int HS, int BV, int WHICH>
+__device__ __forceinline__ void tile_terms(const double2 (&a)[16], const double2 *__restrict__ tile, unsigned pidx,
+                                           unsigned v0, unsigned rep, uint32_t k, uint32_t count,
+                                           const TileTerm *terms, double &acc) {
+    TileTermRaw t = load_term(terms, k);
+    double w[8];
 #pragma unroll
-    for (int i = 0; i < NA; ++i) { fe[i] = 0.0; go[i] = 0.0; }
-    uint32_t k = g.kb;
-    for (uint32_t e = 0; e < g.n_even; ++e, ++k) {
-        const TileTermRaw t = load_term(terms, k);
-        const unsigned p0 = (unsigned)(__popcll(rep & t.packed) + __popc(v0 & (unsigned)(t.packed >> 40) & 0xffu)) & 1u;
-        const unsigned S = (unsigned)(t.packed >> 48) ^ (0u - p0);
-#pragma unroll
-        for (int i = 0; i < NA; ++i) {
-            const int r = ((i >> HS) << (HS + 1)) | (BV << HS) | (i & ((1 << HS) - 1));
-            fe[i] += flip_bit(t.u, S, r);
-        }
-    }
-    for (uint32_t o = 0; o < g.n_odd; ++o, ++k) {
-        const TileTermRaw t = load_term(terms, k);
-        const unsigned p0 = (unsigned)(__popcll(rep & t.packed) + __popc(v0 & (unsigned)(t.packed >> 40) & 0xffu)) & 1u;
-        const unsigned S = (unsigned)(t.packed >> 48) ^ (0u - p0);
-#pragma unroll
-        for (int i = 0; i < NA; ++i) {
-            const int r = ((i >> HS) << (HS + 1)) | (BV << HS) | (i & ((1 << HS) - 1));
-            go[i] += flip_bit(t.u, S, r);
-        }
-    }
-    const unsigned xr = (unsigned)g.xv >> 8;
-    const unsigned plo = (v0 ^ (unsigned)g.xv) & 0xffu;
-#pragma unroll
-    for (int i = 0; i < NA; ++i) {
+    for (int i = 0; i < 8; ++i) {
         const int r = ((i >> HS) << (HS + 1)) | (BV << HS) | (i & ((1 << HS) - 1));
-        const double2 b = tile[(((unsigned)r ^ xr) << 8) | plo];
-        const double wre = b.x * a[r].x + b.y * a[r].y;
-        const double wim = b.x * a[r].y - b.y * a[r].x;
-        acc[i & 3] += fe[i] * wre + go[i] * wim;
+        const double2 b = tile[pidx ^ ((unsigned)r << 8)];
+        w[i] = WHICH == 0 ? fma(b.x, a[r].x, b.y * a[r].y) : fma(b.x, a[r].y, -(b.y * a[r].x));
+    }
+    for (uint32_t e = 0; e < count; ++e) {
+        const unsigned zl = (unsigned)t.packed;                   // z on the high index bits
+        const unsigned hw = (unsigned)(t.packed >> 32);           // bits 0..7: thread bits of zv, 8..11: register bits
+        const double u = t.u;
+        if (e + 1 < count) t = load_term(terms, k + e + 1);      // prefetch the next term
+        // coset part and thread part share one POPC: parity(a) ^ parity(b) = parity(a ^ b)
+        unsigned par = (unsigned)__popc((rep & zl) ^ (v0 & hw & 0xffu));
+        if (BV) par += hw >> (8 + HS);
+        // free register bits: i-bit k <-> r-bit (k < HS ? k : k + 1)
+        const double s0 = pm_one_hi(hw, 8 + (0 < HS ? 0 : 1));
+        const double s1 = pm_one_hi(hw, 8 + (1 < HS ? 1 : 2));
+        const double s2 = pm_one_hi(hw, 8 + (2 < HS ? 2 : 3));
+        const double us = __hiloint2double(__double2hiint(u) ^ (int)(par << 31), __double2loint(u));
+        acc = fma(us, signed_sum8(w, s0, s1, s2), acc);
     }
 }
 
-__global__ void __launch_bounds__(kBlock, 2)
+template <int HS, int BV>
+__device__ __forceinline__ void tile_group(const double2 (&a)[16], const double2 *__restrict__ tile, unsigned v0,
+                                           unsigned rep, const int4 g, const TileTerm *terms, double &acc) {
+    // g = {kb, n_even, n_odd, xv | hsel << 16}
+    const unsigned pidx = ((unsigned)g.w ^ v0) & 0xfffu;      // partner of register 0; register r: pidx ^ (r << 8)
+    if (g.y) tile_terms<HS, BV, 0>(a, tile, pidx, v0, rep, (uint32_t)g.x, (uint32_t)g.y, terms, acc);
+    if (g.z) tile_terms<HS, BV, 1>(a, tile, pidx, v0, rep, (uint32_t)(g.x + g.y), (uint32_t)g.z, terms, acc);
+}
+
+// all groups [g0, g1) of one pair-selector class
+template <int HS, bool BOTH>
+__device__ __forceinline__ void tile_class(const double2 (&a)[16], const double2 *__restrict__ tile, unsigned v0, unsigned rep,
+                                           const int4 *gp, int g0, int g1, const TileTerm *tp, double &acc) {
+    if (g0 >= g1) return;
+    int4 g = gp[g0];
+    for (int gi = g0; gi < g1; ++gi) {
+        const int4 gc = g;
+        if (gi + 1 < g1) g = gp[gi + 1];        // prefetch the next group record
+        tile_group<HS, 0>(a, tile, v0, rep, gc, tp, acc);
+        if (BOTH) tile_group<HS, 1>(a, tile, v0, rep, gc, tp, acc);
+    }
+}
+
+constexpr int kStageGroups = 64;     // descriptor records staged in shared memory per batch
+constexpr int kStageTerms = 192;
+
+// MINB = resident CTAs per SM the register allocation is held to (2: 128 registers, 3: 80 with a few spills)
+template <int MINB>
+__global__ void __launch_bounds__(kBlock, MINB)
 k_tile_expect(const double2 *__restrict__ psi, int C, int M, const TileBatch *__restrict__ batches, int n_batches,
               unsigned long long tile_begin, unsigned long long tile_count, const TileGroup *__restrict__ groups,
               const TileTerm *__restrict__ terms, double *partials, unsigned *counter, double *out) {
     extern __shared__ __align__(16) unsigned char tile_raw[];
     double2 *tile = reinterpret_cast<double2 *>(tile_raw);
     __shared__ TileBatch sb;
+    __shared__ __align__(16) int4 s_groups[kStageGroups];
+    __shared__ __align__(16) double2 s_terms[kStageTerms];
     const unsigned v0 = threadIdx.x;
     const unsigned lo = v0 & ((1u << C) - 1u);
-    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+    double acc = 0.0;
     int cur_b = -1;
-    unsigned long long Tc = 0, rb0 = 0, rb1 = 0, rb2 = 0, rb3 = 0;
+    unsigned Tc = 0, rb0 = 0, rb1 = 0, rb2 = 0, rb3 = 0;
+    const double2 *psi_lo = psi + lo;
+    const unsigned chunk_stride = 1u << C;
+    const int4 *gp = nullptr;            // group records of the current batch, indexed from 0
+    const TileTerm *tp = nullptr;        // term records, indexed by (kb - kb0)
+    int n_g = 0, c0 = 0, c1 = 0, c2 = 0, c3 = 0;
     const unsigned long long total = (unsigned long long)n_batches * tile_count;
 
     for (unsigned long long w = blockIdx.x; w < total; w += gridDim.x) {
@@ -100,43 +141,49 @@ k_tile_expect(const double2 *__restrict__ psi, int C, int M, const TileBatch *__
             Tc = 0;
             for (int i = 0; i < 8 - C; ++i) if ((v0 >> (C + i)) & 1u) Tc ^= sb.basis[i];
             rb0 = sb.basis[M - 4]; rb1 = sb.basis[M - 3]; rb2 = sb.basis[M - 2]; rb3 = sb.basis[M - 1];
+            n_g = sb.g_end - sb.g_begin;
+            c0 = sb.cls_end[0]; c1 = sb.cls_end[1]; c2 = sb.cls_end[2]; c3 = sb.cls_end[3];
+            const uint32_t kb0 = (uint32_t)sb.t_begin;
+            const int n_t = sb.t_end - sb.t_begin;
+            const int4 *gsrc = reinterpret_cast<const int4 *>(groups) + sb.g_begin;
+            if (n_g <= kStageGroups && n_t <= kStageTerms) {
+                for (int i = threadIdx.x; i < n_g; i += kBlock) {
+                    int4 g = gsrc[i];
+                    g.x -= (int)kb0;
+                    s_groups[i] = g;
+                }
+                for (int i = threadIdx.x; i < n_t; i += kBlock) s_terms[i] = reinterpret_cast<const double2 *>(terms)[kb0 + i];
+                gp = s_groups;
+                tp = reinterpret_cast<const TileTerm *>(s_terms);
+            } else {
+                gp = gsrc;
+                tp = terms;
+            }
+            __syncthreads();
         }
-        unsigned long long rep = t;
+        unsigned rep = (unsigned)t;             // high index (j >> C) has at most 32 bits
         for (int i = 0; i < M; ++i) {
             const int p = sb.pivot[i];
-            rep = ((rep >> p) << (p + 1)) | (rep & ((1ull << p) - 1ull));
+            rep = ((rep >> p) << (p + 1)) | (rep & ((1u << p) - 1u));
         }
-        const unsigned long long base = rep ^ Tc;
+        const unsigned base = rep ^ Tc;
         double2 a[16];
 #pragma unroll
         for (int r = 0; r < 16; ++r) {
-            const unsigned long long hi = base ^ ((r & 1) ? rb0 : 0ull) ^ ((r & 2) ? rb1 : 0ull) ^ ((r & 4) ? rb2 : 0ull) ^
-                                          ((r & 8) ? rb3 : 0ull);
-            a[r] = psi[(hi << C) | lo];
+            const unsigned hi = base ^ ((r & 1) ? rb0 : 0u) ^ ((r & 2) ? rb1 : 0u) ^ ((r & 4) ? rb2 : 0u) ^ ((r & 8) ? rb3 : 0u);
+            a[r] = __ldcs(psi_lo + (unsigned long long)hi * chunk_stride);     // streamed once per batch
         }
         __syncthreads();                        // readers of the previous tile are done
 #pragma unroll
         for (int r = 0; r < 16; ++r) tile[((unsigned)r << 8) | v0] = a[r];
         __syncthreads();
-        for (int g = sb.g_begin; g < sb.g_end; ++g) {
-            const int4 raw = __ldg(reinterpret_cast<const int4 *>(groups) + g);
-            TileGroup tg;
-            tg.kb = (uint32_t)raw.x; tg.n_even = (uint32_t)raw.y; tg.n_odd = (uint32_t)raw.z;
-            tg.xv = (uint16_t)((unsigned)raw.w & 0xffffu);
-            tg.hsel = (int16_t)((unsigned)raw.w >> 16);
-            switch (tg.hsel) {
-            case 0: tile_group<0, 0>(a, tile, v0, rep, tg, terms, acc); break;
-            case 1: tile_group<1, 0>(a, tile, v0, rep, tg, terms, acc); break;
-            case 2: tile_group<2, 0>(a, tile, v0, rep, tg, terms, acc); break;
-            case 3: tile_group<3, 0>(a, tile, v0, rep, tg, terms, acc); break;
-            default:    // no register bit in xv: visit every amplitude (weight 1), in two halves
-                tile_group<3, 0>(a, tile, v0, rep, tg, terms, acc);
-                tile_group<3, 1>(a, tile, v0, rep, tg, terms, acc);
-                break;
-            }
-        }
+        tile_class<0, false>(a, tile, v0, rep, gp, 0, c0, tp, acc);
+        tile_class<1, false>(a, tile, v0, rep, gp, c0, c1, tp, acc);
+        tile_class<2, false>(a, tile, v0, rep, gp, c1, c2, tp, acc);
+        tile_class<3, false>(a, tile, v0, rep, gp, c2, c3, tp, acc);
+        tile_class<3, true>(a, tile, v0, rep, gp, c3, n_g, tp, acc);   // no register bit in xv: every amplitude, weight 1
     }
-    double v[1] = {(acc[0] + acc[1]) + (acc[2] + acc[3])};
+    double v[1] = {acc};
     grid_reduce<1>(v, partials, counter, out, 1.0);
 }
 

@@ -26,12 +26,16 @@ constexpr int kTileBits = 12;        // tile = 4096 amplitudes = 64 KB of double
 constexpr int kTileRegBits = 4;      // 16 amplitudes per thread (virtual bits 8..11)
 constexpr int kTileMaxDim = 10;      // M = kTileBits - C, C >= 2
 
+constexpr int kTileClasses = 5;      // groups of a batch are ordered by hsel = 0, 1, 2, 3, -1
+
 struct TileBatch {                   // 128 bytes
-    uint64_t basis[kTileMaxDim];     // basis[i] <-> virtual bit C + i; acts on the high index (j >> C)
+    uint32_t basis[kTileMaxDim];     // basis[i] <-> virtual bit C + i; acts on the high index (j >> C), n - C <= 32
     uint8_t pivot[kTileMaxDim];      // pivot positions in the high index, ascending (for coset reps)
-    uint8_t pad0[6];
+    uint8_t pad0[2];
     int32_t g_begin, g_end;          // groups of this batch
-    int32_t pad1[6];
+    int32_t t_begin, t_end;          // terms of this batch
+    int32_t cls_end[kTileClasses];   // end of each hsel class, relative to g_begin
+    int32_t pad1[10];
 };
 static_assert(sizeof(TileBatch) == 128, "TileBatch layout");
 
@@ -45,7 +49,7 @@ struct TileGroup {                   // 16 bytes
 static_assert(sizeof(TileGroup) == 16, "TileGroup layout");
 
 struct TileTerm {                    // 16 bytes
-    uint64_t packed;                 // bits 0..39 z_hi | 40..47 zv & 0xff | 48..63 sign word over the 16 registers
+    uint64_t packed;                 // bits 0..31 z_hi | 32..39 zv & 0xff (thread bits) | 40..43 zv >> 8 (register bits)
     double u;                        // weight * (coef | i*coef): real for a Hermitian H
 };
 static_assert(sizeof(TileTerm) == 16, "TileTerm layout");
@@ -183,17 +187,29 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
         for (int t : top) perm.push_back(t);       // register bits are the top kTileRegBits coordinates
 
         TileBatch B{};
-        for (int i = 0; i < dim; ++i) B.basis[i] = rr.b[perm[i]];
+        for (int i = 0; i < dim; ++i) B.basis[i] = (uint32_t)rr.b[perm[i]];
         std::vector<int> sp(rr.piv.begin(), rr.piv.end());
         std::sort(sp.begin(), sp.end());
         for (int i = 0; i < dim; ++i) B.pivot[i] = (uint8_t)sp[i];
         B.g_begin = (int32_t)P.groups.size();
+        B.t_begin = (int32_t)P.terms.size();
         auto permute_mu = [&](uint64_t m) {
             uint64_t r = 0;
             for (int i = 0; i < dim; ++i) r |= ((m >> perm[i]) & 1ull) << i;
             return r;
         };
-        for (size_t k = 0; k < members.size(); ++k) {
+        // order the members by pair-selector class (hsel 0, 1, 2, 3, then -1): one code path per class on the device
+        auto class_of = [&](size_t k) {
+            const unsigned xr = (unsigned)(((permute_mu(mu[k]) << C) >> (kTileBits - kTileRegBits)) & ((1u << kTileRegBits) - 1));
+            return xr ? 31 - __builtin_clz(xr) : kTileClasses - 1;
+        };
+        std::vector<size_t> ord(members.size());
+        for (size_t k = 0; k < ord.size(); ++k) ord[k] = k;
+        std::stable_sort(ord.begin(), ord.end(), [&](size_t a, size_t b) { return class_of(a) < class_of(b); });
+        for (int c = 0; c < kTileClasses; ++c) B.cls_end[c] = 0;
+        for (size_t kk = 0; kk < members.size(); ++kk) {
+            const size_t k = ord[kk];
+            for (int c = class_of(k); c < kTileClasses; ++c) ++B.cls_end[c];
             const G &g = gs[members[k]];
             const uint64_t m = permute_mu(mu[k]);
             TileGroup tg{};
@@ -206,11 +222,11 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
                 const TilePlanTermIn &ti = in[order[t]];
                 const uint64_t zhi = ti.z >> C;
                 uint64_t Zv = 0;
-                for (int i = 0; i < dim; ++i) Zv |= (uint64_t)parity64h(B.basis[i] & zhi) << i;
+                for (int i = 0; i < dim; ++i) Zv |= (uint64_t)parity64h((uint64_t)B.basis[i] & zhi) << i;
                 const unsigned zv = (unsigned)((Zv << C) | (ti.z & lomask));
                 TileTerm tt;
-                tt.packed = (zhi & ((1ull << 40) - 1)) | ((uint64_t)(zv & 0xffu) << 40) |
-                            ((uint64_t)sign_word16(zv >> (kTileBits - kTileRegBits)) << 48);
+                tt.packed = (zhi & 0xffffffffull) | ((uint64_t)(zv & 0xffu) << 32) |
+                            ((uint64_t)((zv >> (kTileBits - kTileRegBits)) & 0xfu) << 40);
                 tt.u = weight * ti.u;
                 P.terms.push_back(tt);
                 P.term_src.push_back(ti.idx);
@@ -221,6 +237,7 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
             ++n_done;
         }
         B.g_end = (int32_t)P.groups.size();
+        B.t_end = (int32_t)P.terms.size();
         P.batches.push_back(B);
     }
     return P;
