@@ -282,17 +282,29 @@ def run_gpu(args):
     alg_bytes = 16.0 * be.n_local * G
     k_ms = float(np.mean(kernel_ms))
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
-    traffic = None
+    traffic = traffic_tile = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
         try:
-            traffic = json.load(open(tpath)).get("k_expect_energy_bytes_per_step")
+            tj = json.load(open(tpath))
+            traffic = tj.get("k_expect_energy_bytes_per_step")
+            # ncu --set full capture of k_tile_expect on this exact workload (dram__bytes_read.sum + dram__bytes_write.sum, one launch)
+            if tj.get("k_tile_expect", {}).get("n_qubits") == n and tj["k_tile_expect"].get("n_terms") == int(Tn):
+                traffic_tile = tj["k_tile_expect"]["dram_bytes_per_launch"]
         except Exception:
             traffic = None
+    tile = args.engine != "stream"
+    if tile and traffic_tile is not None:
+        traffic = traffic_tile
     roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-            "kernel": "k_expect_energy<8,true>", "peak_source": peak_src,
-            "note": "achieved = 16 B x 2^n_local x G per step / CUDA-event time of the step's k_expect_energy launches "
-                    "(one launch per xmask bucket); the pair form reads each pair once, so DRAM traffic is about half the model"}
+            "kernel": "k_tile_expect<2>" if tile else "k_expect_energy<8,true>", "peak_source": peak_src,
+            "launches_per_step": int(launches // max(1, args.steps)),
+            "note": ("achieved = ALGORITHMIC bytes 16 B x 2^n_local x G (SURVEY.md 8d) / CUDA-event time of the step's single "
+                     "k_tile_expect launch. The tile engine evaluates >= 9 xmask groups per HBM read of the state (GF(2)-subspace "
+                     "tiles in shared memory), so its DRAM traffic is ~16 B x 2^n x n_batches and frac > 1 is expected; the "
+                     "kernel is bound by shared-memory bandwidth and issue, see DESIGN.md") if tile else
+                    ("achieved = 16 B x 2^n_local x G per step / CUDA-event time of the step's k_expect_energy launches "
+                     "(one launch per xmask bucket); the pair form reads each pair once, so DRAM traffic is about half the model")}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",

@@ -11,8 +11,8 @@ import c_oracle as co
 import xaccvqe_b200 as xb
 
 TILE_BITS = 12
-BATCH_DT = np.dtype([("basis", "<u4", 10), ("pivot", "u1", 10), ("pad0", "u1", 2), ("g_begin", "<i4"), ("g_end", "<i4"),
-                     ("t_begin", "<i4"), ("t_end", "<i4"), ("cls_end", "<i4", 5), ("pad1", "<i4", 10)])
+BATCH_DT = np.dtype([("basis", "<u4", 10), ("seg", "<u4", 11), ("g_begin", "<i4"), ("g_end", "<i4"),
+                     ("t_begin", "<i4"), ("t_end", "<i4"), ("cls_end", "<i4", 5), ("pad1", "<i4", 2)])
 GROUP_DT = np.dtype([("kb", "<u4"), ("n_even", "<u4"), ("n_odd", "<u4"), ("xv", "<u2"), ("hsel", "<i2")])
 TERM_DT = np.dtype([("packed", "<u8"), ("u", "<f8")])
 
@@ -52,10 +52,9 @@ def replay(n, c, B, G, T, psi):
         for i in range(M):
             combo ^= np.where((mu >> np.uint64(i)) & np.uint64(1), np.uint64(b["basis"][i]), np.uint64(0)).astype(np.uint64)
         for t in range(n_tiles):
-            rep = t
-            for i in range(M):
-                p = int(b["pivot"][i])
-                rep = ((rep >> p) << (p + 1)) | (rep & ((1 << p) - 1))
+            rep = 0
+            for i in range(11):
+                rep |= (t & int(b["seg"][i])) << i
             j = ((np.uint64(rep) ^ combo) << np.uint64(c)) | lo
             tile = psi[j.astype(np.int64)]
             cls = [int(g["hsel"]) for g in G[b["g_begin"]:b["g_end"]]]

@@ -103,13 +103,24 @@ __device__ __forceinline__ void tile_class(const double2 (&a)[16], const double2
     }
 }
 
+__device__ __forceinline__ unsigned tile_rep(const TileBatch &sb, unsigned t) {
+    unsigned rep = 0;
+#pragma unroll
+    for (int i = 0; i <= kTileMaxDim; ++i) rep |= (t & sb.seg[i]) << i;
+    return rep;
+}
+
+__device__ __forceinline__ void prefetch_l2(const void *p) {
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
+
 constexpr int kStageGroups = 64;     // descriptor records staged in shared memory per batch
 constexpr int kStageTerms = 192;
 
 // MINB = resident CTAs per SM the register allocation is held to (2: 128 registers, 3: 80 with a few spills)
 template <int MINB>
 __global__ void __launch_bounds__(kBlock, MINB)
-k_tile_expect(const double2 *__restrict__ psi, int C, int M, const TileBatch *__restrict__ batches, int n_batches,
+k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_bytes, const TileBatch *__restrict__ batches, int n_batches,
               unsigned long long tile_begin, unsigned long long tile_count, const TileGroup *__restrict__ groups,
               const TileTerm *__restrict__ terms, double *partials, unsigned *counter, double *out) {
     extern __shared__ __align__(16) unsigned char tile_raw[];
@@ -122,8 +133,10 @@ k_tile_expect(const double2 *__restrict__ psi, int C, int M, const TileBatch *__
     double acc = 0.0;
     int cur_b = -1;
     unsigned Tc = 0, rb0 = 0, rb1 = 0, rb2 = 0, rb3 = 0;
-    const double2 *psi_lo = psi + lo;
-    const unsigned chunk_stride = 1u << C;
+    const char *psi_lo = reinterpret_cast<const char *>(psi + lo);   // chunk hi of this thread's column: psi_lo + hi * chunk_bytes
+    unsigned pcA = 0;                    // combo of the two rows this thread prefetches for the next tile
+    unsigned rep_next = 0;
+    bool have_next = false;
     const int4 *gp = nullptr;            // group records of the current batch, indexed from 0
     const TileTerm *tp = nullptr;        // term records, indexed by (kb - kb0)
     int n_g = 0, c0 = 0, c1 = 0, c2 = 0, c3 = 0;
@@ -141,6 +154,9 @@ k_tile_expect(const double2 *__restrict__ psi, int C, int M, const TileBatch *__
             Tc = 0;
             for (int i = 0; i < 8 - C; ++i) if ((v0 >> (C + i)) & 1u) Tc ^= sb.basis[i];
             rb0 = sb.basis[M - 4]; rb1 = sb.basis[M - 3]; rb2 = sb.basis[M - 2]; rb3 = sb.basis[M - 1];
+            // the 8 lanes sharing a 128-byte line split its 16 rows between them: this thread takes rows 2(lane & 7), +1
+            pcA = Tc ^ ((v0 & 1u) ? rb1 : 0u) ^ ((v0 & 2u) ? rb2 : 0u) ^ ((v0 & 4u) ? rb3 : 0u);
+            have_next = false;
             n_g = sb.g_end - sb.g_begin;
             c0 = sb.cls_end[0]; c1 = sb.cls_end[1]; c2 = sb.cls_end[2]; c3 = sb.cls_end[3];
             const uint32_t kb0 = (uint32_t)sb.t_begin;
@@ -161,22 +177,28 @@ k_tile_expect(const double2 *__restrict__ psi, int C, int M, const TileBatch *__
             }
             __syncthreads();
         }
-        unsigned rep = (unsigned)t;             // high index (j >> C) has at most 32 bits
-        for (int i = 0; i < M; ++i) {
-            const int p = sb.pivot[i];
-            rep = ((rep >> p) << (p + 1)) | (rep & ((1u << p) - 1u));
-        }
+        const unsigned rep = have_next ? rep_next : tile_rep(sb, (unsigned)t);   // high index (j >> C) has at most 32 bits
         const unsigned base = rep ^ Tc;
         double2 a[16];
 #pragma unroll
         for (int r = 0; r < 16; ++r) {
             const unsigned hi = base ^ ((r & 1) ? rb0 : 0u) ^ ((r & 2) ? rb1 : 0u) ^ ((r & 4) ? rb2 : 0u) ^ ((r & 8) ? rb3 : 0u);
-            a[r] = __ldcs(psi_lo + (unsigned long long)hi * chunk_stride);     // streamed once per batch
+            a[r] = __ldcs(reinterpret_cast<const double2 *>(psi_lo + (unsigned long long)hi * chunk_bytes));   // streamed once per batch
         }
         __syncthreads();                        // readers of the previous tile are done
 #pragma unroll
         for (int r = 0; r < 16; ++r) tile[((unsigned)r << 8) | v0] = a[r];
         __syncthreads();
+        {   // pull the CTA's next tile into L2 while this one is being worked on: 512 lines, two per thread
+            const unsigned long long wn = w + gridDim.x;
+            have_next = wn < total && wn / tile_count == (unsigned long long)b;
+            if (have_next) {
+                rep_next = tile_rep(sb, (unsigned)(tile_begin + (wn - (unsigned long long)b * tile_count)));
+                const unsigned h0 = rep_next ^ pcA;
+                prefetch_l2(psi_lo + (unsigned long long)h0 * chunk_bytes);
+                prefetch_l2(psi_lo + (unsigned long long)(h0 ^ rb0) * chunk_bytes);
+            }
+        }
         tile_class<0, false>(a, tile, v0, rep, gp, 0, c0, tp, acc);
         tile_class<1, false>(a, tile, v0, rep, gp, c0, c1, tp, acc);
         tile_class<2, false>(a, tile, v0, rep, gp, c1, c2, tp, acc);

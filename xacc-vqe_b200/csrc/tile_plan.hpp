@@ -30,12 +30,11 @@ constexpr int kTileClasses = 5;      // groups of a batch are ordered by hsel = 
 
 struct TileBatch {                   // 128 bytes
     uint32_t basis[kTileMaxDim];     // basis[i] <-> virtual bit C + i; acts on the high index (j >> C), n - C <= 32
-    uint8_t pivot[kTileMaxDim];      // pivot positions in the high index, ascending (for coset reps)
-    uint8_t pad0[2];
+    uint32_t seg[kTileMaxDim + 1];   // coset representative of tile t:  rep = OR_i (t & seg[i]) << i  (zeros at the pivots)
     int32_t g_begin, g_end;          // groups of this batch
     int32_t t_begin, t_end;          // terms of this batch
     int32_t cls_end[kTileClasses];   // end of each hsel class, relative to g_begin
-    int32_t pad1[10];
+    int32_t pad1[2];
 };
 static_assert(sizeof(TileBatch) == 128, "TileBatch layout");
 
@@ -190,7 +189,16 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
         for (int i = 0; i < dim; ++i) B.basis[i] = (uint32_t)rr.b[perm[i]];
         std::vector<int> sp(rr.piv.begin(), rr.piv.end());
         std::sort(sp.begin(), sp.end());
-        for (int i = 0; i < dim; ++i) B.pivot[i] = (uint8_t)sp[i];
+        {   // tile index bits [lo_i, hi_i) move up by i = number of pivots below them
+            int lo = 0;
+            for (int i = 0; i <= dim; ++i) {
+                const int hi = i < dim ? sp[i] - i : 32;
+                uint64_t m = 0;
+                if (hi > lo) m = ((hi >= 32 ? (1ull << 32) : (1ull << hi)) - 1) & ~((1ull << lo) - 1);
+                B.seg[i] = (uint32_t)m;
+                lo = hi;
+            }
+        }
         B.g_begin = (int32_t)P.groups.size();
         B.t_begin = (int32_t)P.terms.size();
         auto permute_mu = [&](uint64_t m) {
