@@ -1,0 +1,92 @@
+"""Sharded register (state split by the high index bits over several GPUs, one process per GPU, NCCL)
+against the CPU oracle.  Needs >= 2 GPUs; skipped otherwise (the round-end single-GPU run skips it,
+`gpurun --gpus 2 -- python -m pytest tests/test_gpu_sharded.py -m gpu` runs it)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _n_gpus():
+    try:
+        import torch
+        return torch.cuda.device_count()
+    except Exception:
+        return 0
+
+
+def _worker(rank, world, comm_id, n, T, seed, engine, lanczos, out_q):
+    for p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import xaccvqe_b200 as xb
+    from test_gpu_parity import random_hamiltonian, random_state
+    xm, zm, cf = random_hamiltonian(n, T, seed)
+    psi = random_state(n, seed + 100)
+    be = xb.Backend(n, device=rank, rank=rank, world=world, comm_id=comm_id)
+    be.set_option("expect-engine", engine)
+    be.n_slots(2)
+    be.set_hamiltonian(xm, zm, cf)
+    lo, cnt = be.first, be.n_local
+    be.upload(psi[lo:lo + cnt])
+    e, per = be.expectation(per_term=True)
+    alpha = be.apply_h(0, 1)
+    hpsi = be.download(1)
+    nrm = be.norm2(0)
+    e0, vec = 0.0, None
+    if lanczos:
+        e0, it, res = be.lanczos_ground(tol=1e-10, max_iter=3000, seed=seed, want_vector=True)
+        vec = be.download(0)
+    out_q.put((rank, e, per, alpha, lo, hpsi, nrm, e0, vec))
+    be.close()
+
+
+@pytest.mark.skipif(_n_gpus() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("n,T,seed,engine,lanczos", [(14, 40, 3, "tile", True), (16, 60, 4, "stream", False),
+                                                     (13, 25, 5, "tile", True), (18, 30, 6, "tile", False)])
+def test_two_shards_match_oracle(n, T, seed, engine, lanczos):
+    import torch.multiprocessing as mp
+
+    import c_oracle as co
+    import xaccvqe_b200 as xb
+    from test_gpu_parity import random_hamiltonian, random_state
+    world = 2
+    comm_id = xb.Backend.comm_unique_id()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, world, comm_id, n, T, seed, engine, lanczos, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=300) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    xm, zm, cf = random_hamiltonian(n, T, seed)
+    psi = random_state(n, seed + 100)
+    scale = np.abs(cf).sum()
+    eo, pero = co.expect(n, xm, zm, cf, psi)
+    ref = co.apply(n, xm, zm, cf, psi)
+    full = np.zeros(1 << n, complex)
+    vec = np.zeros(1 << n, complex)
+    for rank, e, per, alpha, lo, hpsi, nrm, e0, v in res:
+        assert abs(e - eo) < 1e-10 * scale
+        assert np.abs(per - pero.real).max() < 1e-11
+        assert abs(alpha - np.vdot(psi, ref)) < 1e-10 * scale
+        assert abs(nrm - 1.0) < 1e-12
+        full[lo:lo + len(hpsi)] = hpsi
+        if lanczos:
+            vec[lo:lo + len(v)] = v
+    assert np.abs(full - ref).max() < 1e-12 * scale
+    if lanczos:
+        # both ranks report the same eigenvalue; the gathered Ritz vector is an eigenvector
+        assert abs(res[0][7] - res[1][7]) < 1e-12 * scale
+        hv = co.apply(n, xm, zm, cf, vec)
+        assert np.linalg.norm(hv - res[0][7] * vec) < 1e-6 * scale
+        import pauli_oracle as po
+        want, _ = po.ground_state_eigsh(xm, zm, cf, n, tol=1e-13, apply=lambda v: co.apply(n, xm, zm, cf, v))
+        assert abs(res[0][7] - want) < 1e-10 * max(1.0, abs(want))
