@@ -193,6 +193,7 @@ def run_gpu(args):
 
     be = xb.Backend(n, device=local_rank, rank=rank, world=world, comm_id=comm_id)
     be.set_option("expect-engine", args.engine)
+    be.set_option("apply-engine", args.engine)
     be.set_option("tile-chunk-bits", args.chunk_bits)
     be.set_option("tile-ctas-per-sm", args.tile_ctas)
     be.set_hamiltonian(xm, zm, cf)
@@ -207,6 +208,15 @@ def run_gpu(args):
     check_rel = abs(e_prod - want) / max(1.0, float(np.abs(c_plain).sum()))
 
     be.random_state(0, SEED)        # input resident in HBM; 2^28 * 16 B = 4.3 GB >> 126 MB L2
+    apply_op = args.op == "apply"
+    if apply_op:
+        be.n_slots(2)
+
+    def step():
+        if apply_op:
+            be.apply_h(0, 1, want_alpha=False)      # dst = H psi (one Lanczos matrix-vector product)
+            return 0j
+        return be.expectation()
 
     def barrier():
         if world > 1:
@@ -215,14 +225,14 @@ def run_gpu(args):
         be.synchronize()
 
     for _ in range(args.warmup):
-        be.expectation()
+        step()
     barrier()
     l0 = be.kernel_launches()
     kernel_ms = []
     with ClockSampler(local_rank) as clk:
         be.timer_start()
         for _ in range(args.steps):
-            e = be.expectation()
+            e = step()
             kernel_ms.append(be.last_kernel_ms())
         ms = be.timer_stop()
         barrier()
@@ -241,18 +251,20 @@ def run_gpu(args):
         host_np = host.numpy().view(np.complex128)
         be.download(0, out=host_np)
         be.upload(host_np)
-        be.expectation()
+        step()
         be.synchronize()
         t0 = time.perf_counter()
         reps = max(1, min(args.steps, 2))
         for _ in range(reps):
             be.set_hamiltonian(xm, zm, cf)
             be.upload(host_np)
-            e2 = be.expectation()
+            e2 = step()
+            if apply_op:
+                be.download(1, out=host_np)
         be.synchronize()
         dt = (time.perf_counter() - t0) / reps
         e2e = {"value": Tn * N / dt, "unit": UNIT, "h2d_bytes_per_step": int(be.n_local * 16 + T * 32),
-               "d2h_bytes_per_step": 16, "ms_per_step": dt * 1e3}
+               "d2h_bytes_per_step": int(be.n_local * 16) if apply_op else 16, "ms_per_step": dt * 1e3}
         del host
     else:
         host = torch.empty(be.n_local * 2, dtype=torch.float64).pin_memory()
@@ -262,14 +274,16 @@ def run_gpu(args):
         t0 = time.perf_counter()
         be.set_hamiltonian(xm, zm, cf)
         be.upload(host_np)
-        be.expectation()
+        step()
+        if apply_op:
+            be.download(1, out=host_np)
         barrier()
         dt = time.perf_counter() - t0
         tt = torch.tensor([dt], dtype=torch.float64, device="cuda")
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dt = float(tt.item())
         e2e = {"value": Tn * N / dt, "unit": UNIT, "h2d_bytes_per_step": int(be.n_local * 16 + T * 32),
-               "d2h_bytes_per_step": 16, "ms_per_step": dt * 1e3}
+               "d2h_bytes_per_step": int(be.n_local * 16) if apply_op else 16, "ms_per_step": dt * 1e3}
 
     if rank != 0:
         if world > 1:
@@ -279,7 +293,7 @@ def run_gpu(args):
 
     peak, peak_src = measured_peak_gbs()
     # algorithmic bytes of one <psi|H|psi> on one GPU: 16 B x local amplitudes x groups
-    alg_bytes = 16.0 * be.n_local * G
+    alg_bytes = 16.0 * be.n_local * (G + 1 if apply_op else G)
     k_ms = float(np.mean(kernel_ms))
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
     traffic = traffic_tile = None
@@ -293,11 +307,12 @@ def run_gpu(args):
                 traffic_tile = tj["k_tile_expect"]["dram_bytes_per_launch"]
         except Exception:
             traffic = None
-    tile = args.engine != "stream"
+    tile = args.engine == "tile" if apply_op else args.engine != "stream"
     if tile and traffic_tile is not None:
         traffic = traffic_tile
     roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-            "kernel": "k_tile_expect<2>" if tile else "k_expect_energy<8,true>", "peak_source": peak_src,
+            "kernel": ("k_tile_apply" if tile else "k_apply<8,true>") if apply_op else ("k_tile_expect<2>" if tile else "k_expect_energy<8,true>"),
+            "peak_source": peak_src,
             "launches_per_step": int(launches // max(1, args.steps)),
             "note": ("achieved = ALGORITHMIC bytes 16 B x 2^n_local x G (SURVEY.md 8d) / CUDA-event time of the step's single "
                      "k_tile_expect launch. The tile engine evaluates >= 9 xmask groups per HBM read of the state (GF(2)-subspace "
@@ -308,7 +323,7 @@ def run_gpu(args):
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": {"workload": f"synthetic {n}-qubit random Pauli sum, {Tn} terms, fp64 <psi|H|psi>",
+            "config": {"workload": f"synthetic {n}-qubit random Pauli sum, {Tn} terms, fp64 " + ("H.psi" if apply_op else "<psi|H|psi>"),
                        "n_qubits": n, "n_terms": int(Tn), "n_xmask_groups": int(G), "amplitudes_per_gpu": int(be.n_local),
                        "parallelism": f"state sharded over {world} GPU(s) by high index bits",
                        "l2": "inputs larger than L2 (4.3 GB state per GPU vs 126 MB)"},
@@ -334,6 +349,7 @@ def main():
     ap.add_argument("--terms", type=int, default=N_TERMS)
     ap.add_argument("--cpu-terms", type=int, default=24, help="terms in the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--op", default="expect", choices=["expect", "apply"], help="expect: <psi|H|psi> (headline); apply: dst = H psi")
     ap.add_argument("--engine", default="auto", choices=["auto", "tile", "stream"], help="<psi|H|psi> kernel family")
     ap.add_argument("--tile-ctas", type=int, default=2, choices=[2, 3], help="tile engine: resident CTAs per SM")
     ap.add_argument("--chunk-bits", type=int, default=3, help="tile engine: log2 contiguous amplitudes per HBM chunk")

@@ -91,6 +91,8 @@ int b200vqe_destroy(b200vqe_handle h);
 const char *b200vqe_last_error(b200vqe_handle h);
 /* String options in the manner of xacc::setOption(key, value) (e.g. task/tasks/DiagonalizeTask.cpp:15-30).
  *   "expect-engine"   = "auto" | "tile" | "stream"   which <psi|H|psi> kernel set_hamiltonian prepares
+ *   "apply-engine"    = "auto" | "tile" | "stream"   the same for H psi (b200vqe_apply_h, b200vqe_lanczos_ground)
+ *   "tile-ctas-per-sm" = "2" | "3"                   resident CTAs per SM of the tile engine's <psi|H|psi> kernel
  *   "tile-chunk-bits" = "2".."8"                     contiguous amplitudes per HBM chunk of the tile engine
  * Options take effect at the next b200vqe_set_hamiltonian. */
 int b200vqe_set_option(b200vqe_handle h, const char *key, const char *value);

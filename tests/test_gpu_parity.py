@@ -118,6 +118,31 @@ def test_tile_engine_matches_streaming_kernel_and_oracle(xb, n, T, seed, cbits):
     assert abs(got["tile"] - got["stream"]) < REL * scale
 
 
+@pytest.mark.parametrize("n,T,seed,cbits", [(12, 30, 41, 3), (15, 200, 42, 2), (18, 64, 43, 3), (20, 48, 44, 5), (21, 20, 45, 8)])
+def test_tile_apply_matches_streaming_kernel_and_oracle(xb, n, T, seed, cbits):
+    """H psi: tile engine (one launch per batch, read-modify-write of dst) vs streaming kernel vs oracle."""
+    xm, zm, cf = random_hamiltonian(n, T, seed)
+    xm = np.append(xm, np.uint64(0)); zm = np.append(zm, np.uint64(0)); cf = np.append(cf, 0.75)   # identity term rides along
+    psi = random_state(n, seed + 100)
+    ref = co.apply(n, xm, zm, cf, psi)
+    scale = np.abs(cf).sum()
+    outs = {}
+    for engine in ("tile", "stream"):
+        be = xb.Backend(n)
+        be.set_option("apply-engine", engine)
+        be.set_option("tile-chunk-bits", cbits)
+        be.n_slots(2)
+        be.set_hamiltonian(xm, zm, cf)
+        be.upload(psi)
+        be.upload(psi[::-1].copy(), slot=1)          # dst holds garbage: the first batch must overwrite it
+        alpha = be.apply_h(0, 1)
+        outs[engine] = be.download(1)
+        assert np.abs(outs[engine] - ref).max() < 1e-12 * scale, engine
+        assert abs(alpha - np.vdot(psi, ref)) < REL * scale, engine
+        be.close()
+    assert np.abs(outs["tile"] - outs["stream"]).max() < 1e-12 * scale
+
+
 def test_complex_coefficients(xb):
     n = 10
     xm, zm, cf = random_hamiltonian(n, 30, 5, hermitian=False)

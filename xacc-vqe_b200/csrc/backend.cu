@@ -236,6 +236,13 @@ int b200vqe_set_option(b200vqe_handle h, const char *key, const char *value) {
         else FAIL(B200VQE_EINVAL, "expect-engine must be auto, tile or stream");
         return 0;
     }
+    if (k == "apply-engine") {
+        if (v == "auto") h->opt_apply_engine = 0;
+        else if (v == "tile") h->opt_apply_engine = 1;
+        else if (v == "stream") h->opt_apply_engine = 2;
+        else FAIL(B200VQE_EINVAL, "apply-engine must be auto, tile or stream");
+        return 0;
+    }
     if (k == "tile-chunk-bits") {
         const int c = atoi(value);
         if (c < 2 || c > 8) FAIL(B200VQE_EINVAL, "tile-chunk-bits must be in [2, 8]");

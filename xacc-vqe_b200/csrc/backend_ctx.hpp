@@ -39,12 +39,19 @@ struct DeviceHam {
     // tile engine (kernels_tile.cuh): batches of xmask groups evaluated per HBM read of the state
     int tile_C = 0, tile_M = 0, n_tile_batches = 0, n_tile_groups = 0;
     TileBatch *tl_batches = nullptr; TileGroup *tl_groups = nullptr; TileTerm *tl_terms = nullptr;
+    // tile engine for H psi: one plan per x_rank class (which peer slab the partners live in), concatenated
+    struct ApplyClass { int x_rank; int b_begin, b_end; };
+    std::vector<ApplyClass> ta_classes;
+    int ta_C = 0, ta_M = 0, n_ta_batches = 0;
+    TileBatch *ta_batches = nullptr; TileGroup *ta_groups = nullptr; TileTerm *ta_terms = nullptr;
     // host copies for the small-n kernels / stats
     std::vector<GroupDesc> h_gd_a; std::vector<uint64_t> h_tz_a; std::vector<double2> h_tv_a;
 
     void free_device() {
         cudaFree(gd_e); cudaFree(tz_e); cudaFree(tu_e); cudaFree(gd_a); cudaFree(tz_a); cudaFree(tv_a);
         cudaFree(tl_batches); cudaFree(tl_groups); cudaFree(tl_terms);
+        cudaFree(ta_batches); cudaFree(ta_groups); cudaFree(ta_terms);
+        ta_batches = nullptr; ta_groups = nullptr; ta_terms = nullptr;
         gd_e = gd_a = nullptr; tz_e = tz_a = nullptr; tu_e = tv_a = nullptr;
         tl_batches = nullptr; tl_groups = nullptr; tl_terms = nullptr;
     }
@@ -69,6 +76,7 @@ struct b200vqe_ctx {
     double last_ms = 0.0;
     // options (string keys as in the reference's xacc::setOption map)
     int opt_expect_engine = 0;          // 0 auto, 1 tile engine, 2 streaming kernel
+    int opt_apply_engine = 0;           // same, for H psi
     int opt_tile_ctas = 2;              // resident CTAs per SM of the tile engine (2 or 3)
     int opt_tile_chunk_bits = 3;        // C: contiguous amplitudes per chunk = 2^C (128 B at C = 3)
 };

@@ -122,6 +122,20 @@ k_inner(const double2 *__restrict__ bra, const double2 *__restrict__ ket, uint64
     grid_reduce<2>(v, partials, counter, out, 1.0);
 }
 
+// alpha = in_scale * Re <src|dst>  (the tile-engine H psi leaves alpha to this pass; in_scale = 1 / *norm_src)
+__global__ void __launch_bounds__(kBlock, 4)
+k_alpha(const double2 *__restrict__ src, const double2 *__restrict__ dst, uint64_t n, const double *norm_src,
+        double *partials, unsigned *counter, double *out) {
+    const double in_scale = norm_src ? 1.0 / *norm_src : 1.0;
+    double re = 0.0;
+    for (uint64_t j = (uint64_t)blockIdx.x * kBlock + threadIdx.x; j < n; j += (uint64_t)gridDim.x * kBlock) {
+        const double2 a = src[j], b = dst[j];
+        re += a.x * b.x + a.y * b.y;
+    }
+    double v[1] = {re};
+    grid_reduce<1>(v, partials, counter, out, in_scale);
+}
+
 // K4  W_{j+1} = w' - (alpha_j / beta_j) W_j ;  out[0] = ||W_{j+1}||^2 (sqrt taken by k_sqrt)
 //     optional Ritz accumulation  y += (s_j / beta_j) W_j
 __global__ void __launch_bounds__(kBlock, 4)

@@ -15,6 +15,10 @@
 #include "kernels.cuh"
 #include "tile_plan.hpp"
 
+#ifndef B200VQE_APPLY_NR
+#define B200VQE_APPLY_NR 4      // registers of a thread handled per pass over a group's terms in k_tile_apply (4 or 8)
+#endif
+
 namespace b200vqe {
 
 __device__ __forceinline__ double flip_bit(double v, unsigned word, int r) {
@@ -207,6 +211,150 @@ k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_byte
     }
     double v[1] = {acc};
     grid_reduce<1>(v, partials, counter, out, 1.0);
+}
+
+// ---------------------------------------------------------------------------------------------
+// K2 on the tile engine:  dst (+)= in_scale * sum_{groups of ONE batch} f_g(j ^ x_g) src[j ^ x_g]
+//
+// One launch per batch (stream order makes batch b's read-modify-write of dst see batch b-1's).  The tile of src is
+// staged in shared memory exactly as in k_tile_expect; a thread keeps 16 complex accumulators for its own 16 outputs,
+// walks every group of the batch (16 conflict-free LDS.128 per group), and adds the tile's contribution to dst once.
+// HBM traffic per batch: 16 B (src) + 32 B (dst read + write) per amplitude instead of 16 B per GROUP.
+// Signs are evaluated at the thread's own index j (s(j ^ x) = s(j) (-1)^nY is folded into the coefficient on the
+// host): u = coef for even nY, -Im(coef) for odd nY.
+//   first != 0:  dst = in_scale * acc - prev_scale * dst   (prev_scale = 0 unless fuse_prev)   [Lanczos: w' = H v_j - beta_j v_{j-1}]
+//   first == 0:  dst += in_scale * acc
+// ---------------------------------------------------------------------------------------------
+template <int PART, int NR, int WHICH>      // registers [PART*NR, PART*NR + NR)
+__device__ __forceinline__ void apply_terms(double2 (&acc)[16], const double2 *__restrict__ tile, unsigned pidx, unsigned v0,
+                                            unsigned rep, uint32_t k, uint32_t count, const TileTerm *terms) {
+    TileTermRaw t = load_term(terms, k);
+    double2 b[NR];
+#pragma unroll
+    for (int i = 0; i < NR; ++i) b[i] = tile[pidx ^ ((unsigned)(PART * NR + i) << 8)];
+    double f[NR];
+#pragma unroll
+    for (int i = 0; i < NR; ++i) f[i] = 0.0;
+    for (uint32_t e = 0; e < count; ++e) {
+        const unsigned zl = (unsigned)t.packed;
+        const unsigned hw = (unsigned)(t.packed >> 32);
+        const double u = t.u;
+        if (e + 1 < count) t = load_term(terms, k + e + 1);
+        const unsigned par = (unsigned)__popc((rep & zl) ^ (v0 & hw & 0xffu)) & 1u;
+        const unsigned S = (hw >> 16) ^ (0u - par);            // bit r: sign of this term at register r
+#pragma unroll
+        for (int i = 0; i < NR; ++i) f[i] += flip_bit(u, S, PART * NR + i);
+    }
+#pragma unroll
+    for (int i = 0; i < NR; ++i) {
+        const int r = PART * NR + i;
+        if (WHICH == 0) {            // even nY: real factor
+            acc[r].x = fma(f[i], b[i].x, acc[r].x);
+            acc[r].y = fma(f[i], b[i].y, acc[r].y);
+        } else {                     // odd nY: factor i * f
+            acc[r].x = fma(-f[i], b[i].y, acc[r].x);
+            acc[r].y = fma(f[i], b[i].x, acc[r].y);
+        }
+    }
+}
+
+template <int WHICH>
+__device__ __forceinline__ void apply_pass(double2 (&acc)[16], const double2 *__restrict__ tile, unsigned pidx, unsigned v0,
+                                           unsigned rep, uint32_t k, uint32_t count, const TileTerm *terms) {
+    constexpr int NR = B200VQE_APPLY_NR;
+#pragma unroll
+    for (int part = 0; part < 16 / NR; ++part) {
+        if (part == 0) apply_terms<0, NR, WHICH>(acc, tile, pidx, v0, rep, k, count, terms);
+        if (part == 1) apply_terms<1 % (16 / NR), NR, WHICH>(acc, tile, pidx, v0, rep, k, count, terms);
+        if (part == 2) apply_terms<2 % (16 / NR), NR, WHICH>(acc, tile, pidx, v0, rep, k, count, terms);
+        if (part == 3) apply_terms<3 % (16 / NR), NR, WHICH>(acc, tile, pidx, v0, rep, k, count, terms);
+    }
+}
+
+__global__ void __launch_bounds__(kBlock, 2)
+k_tile_apply(const double2 *__restrict__ src, double2 *__restrict__ dst, int C, int M, unsigned chunk_bytes,
+             const TileBatch *__restrict__ batch, unsigned tile_count, const TileGroup *__restrict__ groups,
+             const TileTerm *__restrict__ terms, int first, const double *norm_src, const double *norm_prev, int fuse_prev) {
+    extern __shared__ __align__(16) unsigned char tile_raw[];
+    double2 *tile = reinterpret_cast<double2 *>(tile_raw);
+    __shared__ TileBatch sb;
+    __shared__ __align__(16) int4 s_groups[kStageGroups];
+    __shared__ __align__(16) double2 s_terms[kStageTerms];
+    const unsigned v0 = threadIdx.x;
+    const unsigned lo = v0 & ((1u << C) - 1u);
+    if (threadIdx.x < 32) reinterpret_cast<uint32_t *>(&sb)[threadIdx.x] = reinterpret_cast<const uint32_t *>(batch)[threadIdx.x];
+    __syncthreads();
+    unsigned Tc = 0;
+    for (int i = 0; i < 8 - C; ++i) if ((v0 >> (C + i)) & 1u) Tc ^= sb.basis[i];
+    const unsigned rb0 = sb.basis[M - 4], rb1 = sb.basis[M - 3], rb2 = sb.basis[M - 2], rb3 = sb.basis[M - 1];
+    const int n_g = sb.g_end - sb.g_begin;
+    const uint32_t kb0 = (uint32_t)sb.t_begin;
+    const int n_t = sb.t_end - sb.t_begin;
+    const int4 *gp = reinterpret_cast<const int4 *>(groups) + sb.g_begin;
+    const TileTerm *tp = terms;
+    if (n_g <= kStageGroups && n_t <= kStageTerms) {
+        for (int i = threadIdx.x; i < n_g; i += kBlock) {
+            int4 g = gp[i];
+            g.x -= (int)kb0;
+            s_groups[i] = g;
+        }
+        for (int i = threadIdx.x; i < n_t; i += kBlock) s_terms[i] = reinterpret_cast<const double2 *>(terms)[kb0 + i];
+        gp = s_groups;
+        tp = reinterpret_cast<const TileTerm *>(s_terms);
+    }
+    __syncthreads();
+    const double in_scale = norm_src ? 1.0 / *norm_src : 1.0;
+    const double prev_scale = fuse_prev ? (*norm_src) / (*norm_prev) : 0.0;
+    const char *src_lo = reinterpret_cast<const char *>(src + lo);
+    char *dst_lo = reinterpret_cast<char *>(dst + lo);
+
+    for (unsigned t = blockIdx.x; t < tile_count; t += gridDim.x) {
+        const unsigned rep = tile_rep(sb, t);
+        const unsigned base = rep ^ Tc;
+        {
+            double2 a[16];
+#pragma unroll
+            for (int r = 0; r < 16; ++r) {
+                const unsigned hi = base ^ ((r & 1) ? rb0 : 0u) ^ ((r & 2) ? rb1 : 0u) ^ ((r & 4) ? rb2 : 0u) ^ ((r & 8) ? rb3 : 0u);
+                a[r] = __ldcs(reinterpret_cast<const double2 *>(src_lo + (unsigned long long)hi * chunk_bytes));
+            }
+            __syncthreads();
+#pragma unroll
+            for (int r = 0; r < 16; ++r) tile[((unsigned)r << 8) | v0] = a[r];
+        }
+        __syncthreads();
+        double2 acc[16];
+#pragma unroll
+        for (int r = 0; r < 16; ++r) acc[r] = make_double2(0.0, 0.0);
+        if (n_g) {
+            int4 g = gp[0];
+            for (int gi = 0; gi < n_g; ++gi) {
+                const int4 gc = g;
+                if (gi + 1 < n_g) g = gp[gi + 1];
+                const unsigned pidx = ((unsigned)gc.w ^ v0) & 0xfffu;
+                if (gc.y) apply_pass<0>(acc, tile, pidx, v0, rep, (uint32_t)gc.x, (uint32_t)gc.y, tp);
+                if (gc.z) apply_pass<1>(acc, tile, pidx, v0, rep, (uint32_t)(gc.x + gc.y), (uint32_t)gc.z, tp);
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+            const unsigned hi = base ^ ((r & 1) ? rb0 : 0u) ^ ((r & 2) ? rb1 : 0u) ^ ((r & 4) ? rb2 : 0u) ^ ((r & 8) ? rb3 : 0u);
+            double2 *p = reinterpret_cast<double2 *>(dst_lo + (unsigned long long)hi * chunk_bytes);
+            double2 o = make_double2(acc[r].x * in_scale, acc[r].y * in_scale);
+            if (first) {
+                if (fuse_prev) {
+                    const double2 q = *p;
+                    o.x -= prev_scale * q.x;
+                    o.y -= prev_scale * q.y;
+                }
+            } else {
+                const double2 q = *p;
+                o.x += q.x;
+                o.y += q.y;
+            }
+            *p = o;
+        }
+    }
 }
 
 }  // namespace b200vqe

@@ -49,6 +49,7 @@ static_assert(sizeof(TileGroup) == 16, "TileGroup layout");
 
 struct TileTerm {                    // 16 bytes
     uint64_t packed;                 // bits 0..31 z_hi | 32..39 zv & 0xff (thread bits) | 40..43 zv >> 8 (register bits)
+                                     // | 48..63 sign word: bit r = parity(r & (zv >> 8)), r = 0..15
     double u;                        // weight * (coef | i*coef): real for a Hermitian H
 };
 static_assert(sizeof(TileTerm) == 16, "TileTerm layout");
@@ -100,7 +101,8 @@ inline uint16_t sign_word16(unsigned zr) {   // bit r = parity(r & zr), r = 0..1
 }  // namespace tileplan
 
 // terms: non-identity terms with u already set (coef or i*coef, real part).  Groups of equal x.
-inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> &in) {
+// pair_weights: expectation plans double the coefficients of groups evaluated once per pair; apply plans do not.
+inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> &in, bool pair_weights = true) {
     using namespace tileplan;
     TilePlan P;
     P.n = n; P.C = C; P.M = kTileBits - C;
@@ -234,8 +236,9 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
                 const unsigned zv = (unsigned)((Zv << C) | (ti.z & lomask));
                 TileTerm tt;
                 tt.packed = (zhi & 0xffffffffull) | ((uint64_t)(zv & 0xffu) << 32) |
-                            ((uint64_t)((zv >> (kTileBits - kTileRegBits)) & 0xfu) << 40);
-                tt.u = weight * ti.u;
+                            ((uint64_t)((zv >> (kTileBits - kTileRegBits)) & 0xfu) << 40) |
+                            ((uint64_t)sign_word16((zv >> (kTileBits - kTileRegBits)) & 0xfu) << 48);
+                tt.u = (pair_weights ? weight : 1.0) * ti.u;
                 P.terms.push_back(tt);
                 P.term_src.push_back(ti.idx);
                 ti.odd ? ++tg.n_odd : ++tg.n_even;
