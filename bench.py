@@ -23,6 +23,9 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# NCCL writes its banner ("NCCL version ...") to stdout at NCCL_DEBUG=VERSION/INFO; stdout carries exactly one JSON line
+if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION", "INFO"):
+    os.environ["NCCL_DEBUG"] = "WARN"
 
 METRIC = "H.psi term.amplitude updates/s"
 UNIT = "updates/s"
