@@ -265,6 +265,37 @@ def test_text_fixture_ground_states(xb, golden):
         assert rel(e0, want) < REL, key
 
 
+@pytest.mark.parametrize("n,ne", [(4, 2), (8, 4)])
+def test_sweep_energies_shared_memory_path_matches_per_vector_path(xb, golden, n, ne):
+    """b200vqe_sweep_energies (k_sweep_small: one CTA per parameter vector, state resident in shared memory) against
+    the launch-per-rotation path and the oracle, incl. registers padded to 12 qubits."""
+    if n == 4:
+        op = xb.OpHandle.from_fermion_source(golden["h2_source"], "jw")
+        xm, zm, cf = op.pack()
+    else:
+        xm, zm, cf = random_hamiltonian(n, 60, 90)
+        xm = np.append(xm, np.uint64(0)); zm = np.append(zm, np.uint64(0)); cf = np.append(cf, -0.5)     # identity term
+    x, z, ic, pa, npar = xb.uccsd_rotations(n, ne, "jw")
+    rng = np.random.default_rng(n)
+    thetas = rng.uniform(-0.3, 0.3, size=(7, npar))
+    thetas[3] = 0.0                                      # all rotations skipped
+    be = xb.Backend(n)
+    be.set_hamiltonian(xm, zm, cf)
+    basis = (1 << ne) - 1
+    got = be.sweep_energies(basis, x, z, ic, pa, npar, thetas)
+    for v, th in enumerate(thetas):
+        be.reset(0, basis)
+        be.apply_pauli_rotations(x, z, ic * th[pa])
+        e = be.expectation().real
+        psi = np.zeros(1 << n, complex)
+        psi[basis] = 1
+        for xx, zz, p in zip(x, z, ic * th[pa]):
+            co.pauli_rotation(n, int(xx), int(zz), float(p), psi)
+        eo, _ = co.expect(n, xm, zm, cf, psi)
+        assert abs(got[v] - e) < 1e-12 * np.abs(cf).sum()
+        assert abs(got[v] - eo.real) < REL * np.abs(cf).sum()
+
+
 def test_errors_are_loud(xb):
     be = xb.Backend(4)
     with pytest.raises(xb.B200Error):

@@ -44,6 +44,9 @@ struct DeviceHam {
     std::vector<ApplyClass> ta_classes;
     int ta_C = 0, ta_M = 0, n_ta_batches = 0;
     TileBatch *ta_batches = nullptr; TileGroup *ta_groups = nullptr; TileTerm *ta_terms = nullptr;
+    // natural-layout plan for the shared-memory sweep kernel (registers of up to kTileBits qubits)
+    bool has_sweep_plan = false;
+    TileBatch *sw_batch = nullptr; TileGroup *sw_groups = nullptr; TileTerm *sw_terms = nullptr;
     // host copies for the small-n kernels / stats
     std::vector<GroupDesc> h_gd_a; std::vector<uint64_t> h_tz_a; std::vector<double2> h_tv_a;
 
@@ -51,6 +54,8 @@ struct DeviceHam {
         cudaFree(gd_e); cudaFree(tz_e); cudaFree(tu_e); cudaFree(gd_a); cudaFree(tz_a); cudaFree(tv_a);
         cudaFree(tl_batches); cudaFree(tl_groups); cudaFree(tl_terms);
         cudaFree(ta_batches); cudaFree(ta_groups); cudaFree(ta_terms);
+        cudaFree(sw_batch); cudaFree(sw_groups); cudaFree(sw_terms);
+        sw_batch = nullptr; sw_groups = nullptr; sw_terms = nullptr;
         ta_batches = nullptr; ta_groups = nullptr; ta_terms = nullptr;
         gd_e = gd_a = nullptr; tz_e = tz_a = nullptr; tu_e = tv_a = nullptr;
         tl_batches = nullptr; tl_groups = nullptr; tl_terms = nullptr;

@@ -102,7 +102,9 @@ inline uint16_t sign_word16(unsigned zr) {   // bit r = parity(r & zr), r = 0..1
 
 // terms: non-identity terms with u already set (coef or i*coef, real part).  Groups of equal x.
 // pair_weights: expectation plans double the coefficients of groups evaluated once per pair; apply plans do not.
-inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> &in, bool pair_weights = true) {
+// natural (n == kTileBits only): one batch whose virtual index equals the amplitude index (basis = unit vectors in order),
+// for kernels that keep the whole register in shared memory in its natural order (k_sweep_small).
+inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> &in, bool pair_weights = true, bool natural = false) {
     using namespace tileplan;
     TilePlan P;
     P.n = n; P.C = C; P.M = kTileBits - C;
@@ -138,6 +140,10 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
         // ---- choose the subspace: greedy over the next unassigned groups ----
         Rref rr;
         size_t scanned = 0;
+        if (natural) {
+            // unit vectors inserted from the top bit down stay unit vectors: basis index i <-> high bit nh-1-i
+            for (int p = nh - 1; p >= 0; --p) rr.insert(1ull << p);
+        }
         for (size_t g = cursor; g < NG && (int)rr.b.size() < M && scanned < 8192; ++g) {
             if (done[g]) continue;
             ++scanned;
@@ -184,8 +190,13 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
             top.push_back(best);
             for (size_t k = 0; k < members.size(); ++k) if ((mu[k] >> best) & 1) covered[k] = 1;
         }
-        for (int i = 0; i < dim; ++i) if (!used[i]) perm.push_back(i);
-        for (int t : top) perm.push_back(t);       // register bits are the top kTileRegBits coordinates
+        if (natural) {
+            perm.clear();
+            for (int i = 0; i < dim; ++i) perm.push_back(dim - 1 - i);     // virtual bit C+i <-> high bit i
+        } else {
+            for (int i = 0; i < dim; ++i) if (!used[i]) perm.push_back(i);
+            for (int t : top) perm.push_back(t);       // register bits are the top kTileRegBits coordinates
+        }
 
         TileBatch B{};
         for (int i = 0; i < dim; ++i) B.basis[i] = (uint32_t)rr.b[perm[i]];
