@@ -112,6 +112,11 @@ int b200vqe_debug_tile_plan(int n_qubits, int chunk_bits, int64_t n_terms, const
                             const double *coef_re, const double *coef_im, int64_t *n_batches, int64_t *n_groups,
                             int64_t *n_plan_terms, void *batches, void *groups, void *terms);
 
+/* Host-only: slab and tile-engine share of `rank` in a register sharded over `world` ranks (what
+ * b200vqe_create_sharded / b200vqe_expectation use).  No device needed. */
+int b200vqe_debug_shard_layout(int n_qubits, int rank, int world, uint64_t *n_local, uint64_t *first_index,
+                               uint64_t *tile_begin, uint64_t *tile_count);
+
 /* State */
 int b200vqe_state_reset(b200vqe_handle h, int slot, uint64_t basis_index);
 int b200vqe_state_upload(b200vqe_handle h, int slot, const double *amps, uint64_t first, uint64_t count);

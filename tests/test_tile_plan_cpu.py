@@ -39,10 +39,11 @@ def parity(a):
     return (a & np.uint64(1)).astype(np.int64)
 
 
-def replay(n, c, B, G, T, psi):
-    """What k_tile_expect computes, vectorised over (tile, thread, register)."""
+def replay(n, c, B, G, T, psi, tile_begin=0, tile_count=None):
+    """What k_tile_expect computes, vectorised over (tile, thread, register), for tiles [tile_begin, tile_begin + tile_count)."""
     M = TILE_BITS - c
     n_tiles = 1 << (n - TILE_BITS)
+    tile_count = n_tiles if tile_count is None else tile_count
     v = np.arange(1 << TILE_BITS, dtype=np.uint64)          # virtual index: r<<8 | thread
     mu = v >> np.uint64(c)
     lo = v & np.uint64((1 << c) - 1)
@@ -51,7 +52,7 @@ def replay(n, c, B, G, T, psi):
         combo = np.zeros(1 << TILE_BITS, np.uint64)
         for i in range(M):
             combo ^= np.where((mu >> np.uint64(i)) & np.uint64(1), np.uint64(b["basis"][i]), np.uint64(0)).astype(np.uint64)
-        for t in range(n_tiles):
+        for t in range(tile_begin, tile_begin + tile_count):
             rep = 0
             for i in range(11):
                 rep |= (t & int(b["seg"][i])) << i

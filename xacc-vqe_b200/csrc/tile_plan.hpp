@@ -64,6 +64,15 @@ struct TilePlan {
     std::vector<int64_t> term_src;   // plan term -> index into the input array
 };
 
+// Which tiles (cosets) of every batch a rank of a sharded register evaluates in <psi|H|psi>: a contiguous 1/world share;
+// registers with fewer tiles than ranks are evaluated by rank 0 alone.  The union over ranks is every tile exactly once.
+inline void shard_tile_range(int n, int rank, int world, uint64_t &begin, uint64_t &count) {
+    const uint64_t all = 1ull << (n - kTileBits);
+    const uint64_t per = all / (uint64_t)world;
+    if (per) { begin = per * (uint64_t)rank; count = per; }
+    else { begin = 0; count = rank == 0 ? all : 0; }
+}
+
 namespace tileplan {
 
 inline int parity64h(uint64_t v) { return __builtin_popcountll(v) & 1; }
