@@ -146,7 +146,7 @@ def run_reference(args):
         return
     n = N_QUBITS_1GPU       # host RAM bounds the CPU arm to the 1-GPU register
     xm, zm, cf, _ = synth_pauli_sum(n, N_TERMS, SEED)
-    sample_terms = 24
+    sample_terms = args.cpu_terms
     vals, times = [], []
     base = None
     for i in range(args.warmup + args.steps):
@@ -321,6 +321,8 @@ def run_gpu(args):
                      "k_tile_expect launch. The tile engine evaluates >= 9 xmask groups per HBM read of the state (GF(2)-subspace "
                      "tiles in shared memory), so its DRAM traffic is ~16 B x 2^n x n_batches and frac > 1 is expected; the "
                      "kernel is bound by shared-memory bandwidth and issue, see DESIGN.md") if tile else
+                    ("achieved = ALGORITHMIC bytes 16 B x 2^n_local x (G + 1) (SURVEY.md 8d: G partner reads + one write) / CUDA-event "
+                     "time of the step's H.psi launch(es)") if apply_op else
                     ("achieved = 16 B x 2^n_local x G per step / CUDA-event time of the step's k_expect_energy launches "
                      "(one launch per xmask bucket); the pair form reads each pair once, so DRAM traffic is about half the model")}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -350,7 +352,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--qubits", type=int, default=N_QUBITS_1GPU, help="qubits per GPU shard (default: the named config)")
     ap.add_argument("--terms", type=int, default=N_TERMS)
-    ap.add_argument("--cpu-terms", type=int, default=24, help="terms in the bounded CPU-baseline sample")
+    ap.add_argument("--cpu-terms", type=int, default=256, help="terms in the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--op", default="expect", choices=["expect", "apply"], help="expect: <psi|H|psi> (headline); apply: dst = H psi")
     ap.add_argument("--engine", default="auto", choices=["auto", "tile", "stream"], help="<psi|H|psi> kernel family")

@@ -90,3 +90,79 @@ def test_two_shards_match_oracle(n, T, seed, engine, lanczos):
         import pauli_oracle as po
         want, _ = po.ground_state_eigsh(xm, zm, cf, n, tol=1e-13, apply=lambda v: co.apply(n, xm, zm, cf, v))
         assert abs(res[0][7] - want) < 1e-10 * max(1.0, abs(want))
+
+
+def _gate_program(n, seed):
+    """A seeded gate list that puts controls / targets / rotations on local AND sharded qubits, plus Pauli rotations
+    whose flip mask reaches the shard bits (UCCSD.cpp:282-352 uses exactly this gate set)."""
+    rng = np.random.default_rng(seed)
+    gates = []
+    names = ["X", "Y", "Z", "H", "Rx", "Ry", "Rz"]
+    for q in range(n):
+        gates.append(("H", (q,), 0.0))
+    for _ in range(40):
+        if rng.random() < 0.4:
+            c, t = rng.choice(n, size=2, replace=False)
+            gates.append(("CNOT", (int(c), int(t)), 0.0))
+        else:
+            gates.append((names[int(rng.integers(len(names)))], (int(rng.integers(n)),), float(rng.uniform(-2, 2))))
+    # every CNOT placement relative to the top (sharded) qubits
+    top = n - 1
+    gates += [("CNOT", (top, 0), 0.0), ("CNOT", (1, top), 0.0), ("CNOT", (top, top - 1), 0.0), ("CNOT", (top - 1, top), 0.0),
+              ("Rx", (top,), 0.7), ("Ry", (top,), -0.4), ("Rz", (top,), 1.1), ("X", (top,), 0.0), ("Y", (top,), 0.0),
+              ("Z", (top,), 0.0), ("H", (top,), 0.0), ("H", (top - 1,), 0.0)]
+    rots = []
+    for _ in range(12):
+        x = int(rng.integers(1, 1 << n)) | (1 << top if rng.random() < 0.7 else 0)
+        z = int(rng.integers(0, 1 << n))
+        rots.append((x, z, float(rng.uniform(-1, 1))))
+    return gates, rots
+
+
+def _gate_worker(rank, world, comm_id, n, seed, out_q):
+    for p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import xaccvqe_b200 as xb
+    gates, rots = _gate_program(n, seed)
+    be = xb.Backend(n, device=rank, rank=rank, world=world, comm_id=comm_id)
+    be.reset(0, 5)
+    be.apply_gates(gates)
+    be.apply_pauli_rotations([r[0] for r in rots], [r[1] for r in rots], [r[2] for r in rots])
+    out_q.put((rank, be.first, be.download(0), be.norm2(0)))
+    be.close()
+
+
+@pytest.mark.skipif(_n_gpus() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("world", [2, 4])
+def test_gates_on_sharded_qubits_match_oracle(world):
+    """Ansatz gates and fused Pauli rotations that touch the shard bits (pair exchange over NCCL send/recv)."""
+    import torch.multiprocessing as mp
+
+    import c_oracle as co
+    import xaccvqe_b200 as xb
+    if _n_gpus() < world:
+        pytest.skip("needs %d GPUs" % world)
+    n, seed = 12, 21
+    comm_id = xb.Backend.comm_unique_id()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_gate_worker, args=(r, world, comm_id, n, seed, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=300) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    gates, rots = _gate_program(n, seed)
+    psi = np.zeros(1 << n, complex)
+    psi[5] = 1.0
+    for name, qs, th in gates:
+        co.apply_gate(n, name, qs, th, psi)
+    for x, z, phi in rots:
+        co.pauli_rotation(n, x, z, phi, psi)
+    got = np.zeros(1 << n, complex)
+    for rank, first, amps, nrm in res:
+        got[first:first + len(amps)] = amps
+        assert abs(nrm - 1.0) < 1e-12
+    assert np.abs(got - psi).max() < 1e-12

@@ -97,6 +97,7 @@ static int ensure_slot(b200vqe_ctx *h, int slot) {
 static int ensure_gather(b200vqe_ctx *h) {
     if (h->world == 1 || h->gather) return 0;
     CK(cudaMalloc(&h->gather, (size_t)h->world * h->nloc * sizeof(double2)));
+    if (h->xbuf) { cudaStreamSynchronize(h->stream); cudaFree(h->xbuf); h->xbuf = nullptr; }   // gather now serves the pair exchanges too
     return 0;
 }
 
@@ -111,6 +112,23 @@ static int make_slabs(b200vqe_ctx *h, const double2 *src, Slabs &s) {
     NK(g_nccl.AllGather(src, h->gather, h->nloc * 2, ncclDouble, h->comm, h->stream));
     for (int t = 0; t < h->world; ++t) s.p[t] = h->gather + (size_t)t * h->nloc;
     s.p[h->rank] = src;
+    return 0;
+}
+
+// Pairwise slab exchange for ansatz gates that flip a sharded qubit: this rank's slab goes to `peer` and the peer's
+// arrives in a staging buffer (grouped ncclSend/ncclRecv: the two directions of one NVLink pair run concurrently).
+// Every rank of a pair must call it; pairs are independent, so ranks outside the exchange simply do not call.
+static int exchange_with_peer(b200vqe_ctx *h, const double2 *src, int peer, const double2 **received) {
+    double2 *buf = h->gather;
+    if (!buf) {
+        if (!h->xbuf) CK(cudaMalloc(&h->xbuf, h->nloc * sizeof(double2)));
+        buf = h->xbuf;
+    }
+    NK(g_nccl.GroupStart());
+    NK(g_nccl.Send(src, h->nloc * 2, ncclDouble, peer, h->comm, h->stream));
+    NK(g_nccl.Recv(buf, h->nloc * 2, ncclDouble, peer, h->comm, h->stream));
+    NK(g_nccl.GroupEnd());
+    *received = buf;
     return 0;
 }
 
@@ -194,6 +212,7 @@ int b200vqe_destroy(b200vqe_handle h) {
     cudaStreamSynchronize(h->stream);
     for (auto p : h->slots) if (p) cudaFree(p);
     if (h->gather) cudaFree(h->gather);
+    if (h->xbuf) cudaFree(h->xbuf);
     h->ham.free_device();
     cudaFree(h->partials); cudaFree(h->counter); cudaFree(h->d_out); cudaFreeHost(h->h_out);
     if (h->d_alpha) cudaFree(h->d_alpha);

@@ -71,6 +71,7 @@ struct b200vqe_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_t0 = nullptr, ev_t1 = nullptr;
     std::vector<double2 *> slots;
     double2 *gather = nullptr;          // [world][nloc] staging of the peers' shards
+    double2 *xbuf = nullptr;            // [nloc] staging of ONE peer's shard (ansatz gates on sharded qubits) when gather is absent
     b200vqe::DeviceHam ham;
     double *partials = nullptr; unsigned *counter = nullptr;
     double *d_out = nullptr, *h_out = nullptr;

@@ -253,6 +253,55 @@ k_cnot(double2 *__restrict__ psi, uint64_t nloc, int ctrl, int tgt) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// K3 on sharded qubits.  The flip reaches the shard bits, so every partner of this rank's slab lives in ONE
+// peer's slab (rank ^ x_rank); the host exchanges the two slabs (ncclSend/ncclRecv, NVLink) into `peer`
+// and each rank updates its own amplitudes: 48 bytes per amplitude (own read + write, partner read).
+// ---------------------------------------------------------------------------------------------
+// psi[j] <- c psi[j] + m s(t) peer[j ^ xl],  t = (peer_rank << nl) | (j ^ xl)
+__global__ void __launch_bounds__(kBlock, 4)
+k_pauli_rotation_remote(double2 *__restrict__ psi, const double2 *__restrict__ peer, int nl, int peer_rank, uint64_t xl,
+                        uint64_t z, double c, double mre, double mim) {
+    const uint64_t nloc = 1ull << nl;
+    const uint64_t peer_bits = (uint64_t)peer_rank << nl;
+    for (uint64_t j = (uint64_t)blockIdx.x * kBlock + threadIdx.x; j < nloc; j += (uint64_t)gridDim.x * kBlock) {
+        const uint64_t t = j ^ xl;
+        const double2 a = psi[j], b = __ldcs(peer + t);
+        const unsigned pt = parity64((peer_bits | t) & z);
+        const double tr = flip_sign(mre, pt), ti = flip_sign(mim, pt);
+        psi[j] = make_double2(c * a.x + tr * b.x - ti * b.y, c * a.y + tr * b.y + ti * b.x);
+    }
+}
+
+// one-qubit gate on a shard bit: psi[j] <- m_own psi[j] + m_peer peer[j]   (row of the 2x2 matrix chosen by this rank's bit)
+__global__ void __launch_bounds__(kBlock, 4)
+k_gate1_remote(double2 *__restrict__ psi, const double2 *__restrict__ peer, uint64_t nloc, double ore, double oim, double pre, double pim) {
+    for (uint64_t j = (uint64_t)blockIdx.x * kBlock + threadIdx.x; j < nloc; j += (uint64_t)gridDim.x * kBlock) {
+        const double2 a = psi[j], b = __ldcs(peer + j);
+        psi[j] = make_double2(ore * a.x - oim * a.y + pre * b.x - pim * b.y, ore * a.y + oim * a.x + pre * b.y + pim * b.x);
+    }
+}
+
+// diagonal one-qubit gate on a shard bit: the whole slab takes one phase
+__global__ void __launch_bounds__(kBlock, 4)
+k_scale_complex(double2 *__restrict__ v, uint64_t n, double re, double im) {
+    for (uint64_t j = (uint64_t)blockIdx.x * kBlock + threadIdx.x; j < n; j += (uint64_t)gridDim.x * kBlock) {
+        const double2 a = v[j];
+        v[j] = make_double2(re * a.x - im * a.y, re * a.y + im * a.x);
+    }
+}
+
+// CNOT whose target is a shard bit and whose control is local: amplitudes with the control bit set come from the peer
+__global__ void __launch_bounds__(kBlock, 4)
+k_take_where_bit(double2 *__restrict__ psi, const double2 *__restrict__ peer, uint64_t nloc, int ctrl) {
+    const uint64_t half = nloc >> 1;
+    const uint64_t cb = 1ull << ctrl;
+    for (uint64_t p = (uint64_t)blockIdx.x * kBlock + threadIdx.x; p < half; p += (uint64_t)gridDim.x * kBlock) {
+        const uint64_t j = ((p >> ctrl) << (ctrl + 1)) | (p & (cb - 1)) | cb;
+        psi[j] = __ldcs(peer + j);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // state initialisers
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kBlock, 4)
