@@ -80,6 +80,11 @@ int b200vqe_uccsd_rotations(int n_qubits, int n_electrons, const char *transform
 int b200vqe_uccsd_gates(int n_qubits, int n_electrons, const char *transformation,
                         const double *theta, int n_theta, int64_t *count, b200vqe_gate *gates);
 
+/* Occupation read-out of the diag-number-symmetry branch (task/tasks/DiagonalizeTask.cpp:54-144): rows[i] (n_qubits
+ * entries) such that occupation bit i of basis index j is parity(rows[i] & j).  "jw": unit vectors; "bk": the inverse
+ * over GF(2) of the matrix the reference builds at DiagonalizeTask.cpp:76-121. */
+int b200vqe_number_sector_rows(int n_qubits, const char *transformation, uint64_t *rows);
+
 /* ------------------------------------------------------------------ device backend */
 int b200vqe_create(int n_qubits, int device, b200vqe_handle *out);
 /* Sharded: this process holds amplitudes whose top log2(world) index bits equal rank.
@@ -154,6 +159,14 @@ typedef struct {
 } b200vqe_lanczos_opts;
 int b200vqe_lanczos_ground(b200vqe_handle h, const b200vqe_lanczos_opts *opts, double *eigenvalue,
                            int32_t *iterations, double *residual);
+
+/* Particle-number sector (replaces the diag-number-symmetry branch, task/tasks/DiagonalizeTask.cpp:54-183, options
+ * "diag-number-symmetry" + "n-electrons" + "fermion-transformation"): while set, b200vqe_lanczos_ground diagonalises
+ * P H P, P = projector on the basis states whose occupation vector holds n_electrons ones -- the matrix the reference
+ * assembles at :153-178 whenever H maps the sector into itself.  n_electrons < 0 clears the sector.
+ * b200vqe_state_project_sector applies P to a slot (no renormalisation). */
+int b200vqe_set_number_sector(b200vqe_handle h, int n_electrons, const char *transformation /* "jw" | "bk" */);
+int b200vqe_state_project_sector(b200vqe_handle h, int slot);
 
 /* Batched small-n path: n_vec parameter vectors of a rotation-form ansatz evaluated in one launch,
  * one statevector per CTA resident in shared memory (n <= 13).  energies has n_vec entries.

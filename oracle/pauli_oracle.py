@@ -333,20 +333,77 @@ def diagonalize_reference(op: Op, n: int) -> Tuple[float, np.ndarray]:
     return float(w[0]), v[:, 0]
 
 
-def number_subspace_matrix(op: Op, n: int, n_electrons: int) -> np.ndarray:
-    """diag-number-symmetry branch, JW basis (DiagonalizeTask.cpp:54-72,146-180)."""
+def bk_sector_matrix(n: int) -> np.ndarray:
+    """The GF(2) matrix of DiagonalizeTask.cpp:76-121 ("TranterBK"): Seeley's recursion (:80-104: old block in the two
+    diagonal quadrants, ones in the first row of the upper-right quadrant), bottom-right n x n block when the doubling
+    overshoots (:98-103), then rows and columns reversed (:108-121; the reference's swap loops only terminate for even n)."""
+    B = np.array([[1]], dtype=np.int64)
+    while True:
+        old = B
+        d = old.shape[0]
+        B = np.zeros((2 * d, 2 * d), dtype=np.int64)
+        B[:d, :d] = old
+        B[d:, d:] = old
+        B[0, d:] = 1
+        if B.shape[0] == n:
+            break
+        if B.shape[0] > n:
+            B = B[B.shape[0] - n:, B.shape[1] - n:]
+            break
+    return B[::-1, ::-1].copy()
+
+
+def number_sector_strings(n: int, n_electrons: int, transformation: str = "jw") -> List[str]:
+    """Basis strings of the diag-number-symmetry branch in the reference's enumeration order (DiagonalizeTask.cpp:58-72:
+    std::next_permutation from 0..01..1 = ascending lexicographic), re-encoded y = B x mod 2 for "bk" (:123-141)."""
     import itertools
-    init = "0" * (n - n_electrons) + "1" * n_electrons
-    # std::next_permutation enumerates distinct permutations in lexicographic order
-    strings = sorted(set("".join(p) for p in itertools.permutations(init)))
-    strings = [s for s in strings if s >= init]
+    strings = []
+    for ones in itertools.combinations(range(n), n_electrons):
+        b = ["0"] * n
+        for i in ones:
+            b[i] = "1"
+        strings.append("".join(b))
+    strings.sort()
+    if transformation == "bk":
+        B = bk_sector_matrix(n)
+        out = []
+        for s in strings:
+            x = np.array([1 if ch == "1" else 0 for ch in s], dtype=np.int64)
+            y = (B @ x) % 2
+            out.append("".join("1" if v else "0" for v in y))
+        strings = out
+    return strings
+
+
+def number_subspace_matrix(op: Op, n: int, n_electrons: int, transformation: str = "jw", literal: bool = True) -> np.ndarray:
+    """diag-number-symmetry branch (DiagonalizeTask.cpp:146-178).  literal=True keeps the reference's std::map behaviour:
+    an image OUTSIDE the sector makes bitsToIdx[...] default-insert index 0 (:172), so its coefficient lands in column 0
+    (rows i != 0).  literal=False is the compression P H P.  The two agree whenever H maps the sector into itself."""
+    strings = number_sector_strings(n, n_electrons, transformation)
     idx = {s: i for i, s in enumerate(strings)}
     M = np.zeros((len(strings), len(strings)), dtype=np.complex128)
     for i, s in enumerate(strings):
-        for r, c in action_on_ket(op, s):
+        res = action_on_ket(op, s)
+        for r, c in res:
+            if r == s:
+                M[i, i] += c
+        for r, c in res:
             if r in idx:
-                M[i, idx[r]] += c
+                k = idx[r]
+            elif literal:
+                k = 0
+            else:
+                continue
+            if i != k:
+                M[i, k] += c
     return M
+
+
+def diagonalize_number_symmetry(op: Op, n: int, n_electrons: int, transformation: str = "jw", literal: bool = True) -> float:
+    """eigenvalues(0) of Eigen::SelfAdjointEigenSolver on that matrix (DiagonalizeTask.cpp:179-181); Eigen reads the
+    lower triangle only."""
+    M = number_subspace_matrix(op, n, n_electrons, transformation, literal)
+    return float(np.linalg.eigvalsh(M, UPLO="L")[0])
 
 
 # --------------------------------------------------------------------------

@@ -106,3 +106,21 @@ def test_parse_errors():
         xb.OpHandle.from_fermion_source("__qpu__ k() {\n1.0 0 1 0 0\n}", "nope")
     with pytest.raises(xb.B200Error):
         xb.uccsd_rotations(2, 2, "jw")
+
+
+@pytest.mark.parametrize("n", [2, 4, 6, 8, 12, 14, 16])
+def test_number_sector_rows_bit_exact(n):
+    """b200vqe_number_sector_rows against the oracle's restatement of the GF(2) matrix of DiagonalizeTask.cpp:76-121:
+    the set of basis indices the rows accept equals the set of re-encoded strings the reference enumerates."""
+    assert np.array_equal(xb.capi.number_sector_rows(n, "jw"), np.uint64(1) << np.arange(n, dtype=np.uint64))
+    rows = [int(r) for r in xb.capi.number_sector_rows(n, "bk")]
+    ne = n // 2 if n <= 12 else 2
+    want = set()
+    for s in po.number_sector_strings(n, ne, "bk"):
+        want.add(sum(1 << q for q, ch in enumerate(s) if ch == "1"))     # string position q <-> qubit q <-> index bit q
+    got = {j for j in range(1 << n) if sum(bin(r & j).count("1") & 1 for r in rows) == ne} if n <= 12 else None
+    if got is not None:
+        assert got == want
+    else:
+        for j in want:
+            assert sum(bin(r & j).count("1") & 1 for r in rows) == ne

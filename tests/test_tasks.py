@@ -78,6 +78,21 @@ def test_diagonalize_task_h2_exact(golden):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("tr", ["jw", "bk"])
+def test_diagonalize_task_number_symmetry(golden, tr):
+    """Options diag-number-symmetry + n-electrons (+ fermion-transformation) of DiagonalizeTask.cpp:48-57: the 1-electron
+    sector of H2 lies above the ground state; the 2-electron sector holds it."""
+    import pauli_oracle as po
+    oop, n = po.compile_fermion_source(golden["h2_source"], tr)
+    op = xb.compile(golden["h2_source"], tr)
+    for ne in (1, 2):
+        r = xb.execute(op, None, **{"task": "vqe-diagonalize", "diag-number-symmetry": True, "n-electrons": ne,
+                                    "fermion-transformation": tr})
+        assert abs(r.energy - po.diagonalize_number_symmetry(oop, n, ne, tr)) < 1e-10
+    assert abs(r.energy - golden["h2_ground_energy_exact"]) < 1e-10
+
+
+@pytest.mark.gpu
 def test_compute_energy_task_uccsd(golden):
     """task/tests/ComputeEnergyVQETaskTester.cpp:99-106, python/tests/compute_energy_test.py:41-43."""
     op = xb.compile(golden["h2_source"])

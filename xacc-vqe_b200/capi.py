@@ -170,6 +170,15 @@ def uccsd_rotations(n_qubits: int, n_electrons: int, transformation: str = "jw")
     return xm, zm, ic, pa, npar.value
 
 
+def number_sector_rows(n_qubits: int, transformation: str = "jw"):
+    """rows[i]: occupation bit i of basis index j = parity(rows[i] & j) (task/tasks/DiagonalizeTask.cpp:54-144)."""
+    rows = np.zeros(n_qubits, dtype=np.uint64)
+    rc = lib().b200vqe_number_sector_rows(C.c_int(n_qubits), transformation.encode(), _vp(rows))
+    if rc:
+        raise B200Error(rc, lib().b200vqe_front_error().decode())
+    return rows
+
+
 def uccsd_gates(n_qubits: int, n_electrons: int, theta, transformation: str = "jw"):
     th = _f64(theta)
     cnt = C.c_int64()
@@ -310,6 +319,13 @@ class Backend:
         ev, it, res = C.c_double(), C.c_int32(), C.c_double()
         self._ck(lib().b200vqe_lanczos_ground(self.h, C.byref(o), C.byref(ev), C.byref(it), C.byref(res)))
         return ev.value, it.value, res.value
+
+    def set_number_sector(self, n_electrons: int, transformation: str = "jw"):
+        """diag-number-symmetry (task/tasks/DiagonalizeTask.cpp:54-183): Lanczos runs on P H P; n_electrons < 0 clears."""
+        self._ck(lib().b200vqe_set_number_sector(self.h, C.c_int(n_electrons), transformation.encode()))
+
+    def project_sector(self, slot: int = 0):
+        self._ck(lib().b200vqe_state_project_sector(self.h, C.c_int(slot)))
 
     def sweep_energies(self, basis_index, xmask, zmask, imag_coeff, param, n_params, thetas):
         xm, zm, ic = _u64(xmask), _u64(zmask), _f64(imag_coeff)

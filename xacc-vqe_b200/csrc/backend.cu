@@ -4,6 +4,7 @@
 #include "kernels_apply.cuh"
 #include "kernels_small.cuh"
 #include "kernels_tile.cuh"
+#include "pauli_host.hpp"
 
 #include <algorithm>
 #include <cmath>

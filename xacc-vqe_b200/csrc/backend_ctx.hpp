@@ -80,6 +80,8 @@ struct b200vqe_ctx {
     std::string err;
     int64_t launches = 0;
     double last_ms = 0.0;
+    // particle-number sector (b200vqe_set_number_sector); sector_ne < 0: none
+    int sector_ne = -1; bool sector_unit = true; uint64_t sector_rows[40] = {0};
     // options (string keys as in the reference's xacc::setOption map)
     int opt_expect_engine = 0;          // 0 auto, 1 tile engine, 2 streaming kernel
     int opt_apply_engine = 0;           // same, for H psi

@@ -174,4 +174,13 @@ int b200vqe_uccsd_gates(int n_qubits, int n_electrons, const char *transformatio
     return 0;
 }
 
+// host-only view of the diag-number-symmetry occupation read-out (task/tasks/DiagonalizeTask.cpp:54-144)
+int b200vqe_number_sector_rows(int n_qubits, const char *transformation, uint64_t *rows) {
+    if (!rows) { f_err = "rows is NULL"; return B200VQE_EINVAL; }
+    std::vector<uint64_t> r;
+    if (!number_sector_rows(n_qubits, transformation ? transformation : "jw", r, f_err)) return B200VQE_EINVAL;
+    for (int i = 0; i < n_qubits; ++i) rows[i] = r[i];
+    return 0;
+}
+
 }  // extern "C"

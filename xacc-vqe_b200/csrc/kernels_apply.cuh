@@ -302,6 +302,28 @@ k_take_where_bit(double2 *__restrict__ psi, const double2 *__restrict__ peer, ui
 }
 
 // ---------------------------------------------------------------------------------------------
+// Particle-number sector (diag-number-symmetry, task/tasks/DiagonalizeTask.cpp:54-183): zero every amplitude whose
+// occupation vector x_i = parity(rows[i] & j) does not hold exactly ne ones.  JW: rows are unit vectors, x = j.
+// ---------------------------------------------------------------------------------------------
+struct SectorRows { uint64_t r[40]; };
+
+template <bool UNIT>
+__global__ void __launch_bounds__(kBlock, 4)
+k_project_sector(double2 *__restrict__ psi, uint64_t nloc, uint64_t first, int n, int ne, const __grid_constant__ SectorRows rows) {
+    for (uint64_t j = (uint64_t)blockIdx.x * kBlock + threadIdx.x; j < nloc; j += (uint64_t)gridDim.x * kBlock) {
+        const uint64_t g = first + j;
+        int occ;
+        if (UNIT) {
+            occ = __popcll(g);
+        } else {
+            occ = 0;
+            for (int i = 0; i < n; ++i) occ += (int)parity64(rows.r[i] & g);
+        }
+        if (occ != ne) psi[j] = make_double2(0.0, 0.0);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // state initialisers
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kBlock, 4)

@@ -340,4 +340,50 @@ bool uccsd_rotations(int n_qubits, int n_electrons, const std::string &transform
     return true;
 }
 
+// Occupation read-out of a basis index for the diag-number-symmetry branch (task/tasks/DiagonalizeTask.cpp:54-144).
+// The reference enumerates occupation strings with n_electrons ones (:58-72) and, for "bk", re-encodes each with the
+// GF(2) matrix B built at :76-121 (Seeley's recursion :80-104, bottom-right n x n block :98-103, then rows and
+// columns reversed :108-121): y = B x mod 2 (:125-141), string position i <-> qubit i.  The device needs the converse:
+// is basis index j (bit q = y_q) in the sector?  x = B^-1 y, i.e. x_i = parity(rows[i] & j), rows = B^-1 over GF(2).
+bool number_sector_rows(int n, const std::string &transformation, std::vector<uint64_t> &rows, std::string &err) {
+    if (n < 1 || n > 63) { err = "n_qubits must be in [1, 63]"; return false; }
+    rows.assign(n, 0);
+    if (transformation != "bk") {            // "jw" and everything else: the index is the occupation vector (:74 only tests "bk")
+        for (int i = 0; i < n; ++i) rows[i] = 1ull << i;
+        return true;
+    }
+    // Seeley matrix by doubling: old block on the diagonal quadrants, ones in the first row of the upper-right quadrant
+    int dim = 1;
+    std::vector<std::vector<uint8_t>> B(1, std::vector<uint8_t>(1, 1));
+    do {
+        std::vector<std::vector<uint8_t>> nb(2 * dim, std::vector<uint8_t>(2 * dim, 0));
+        for (int r = 0; r < dim; ++r)
+            for (int c = 0; c < dim; ++c) nb[r][c] = nb[dim + r][dim + c] = B[r][c];
+        for (int c = 0; c < dim; ++c) nb[0][dim + c] = 1;
+        B.swap(nb);
+        dim *= 2;
+    } while (dim < n);
+    const int off = dim - n;                 // bottom-right n x n block (no-op when dim == n)
+    // reversing rows and columns (the reference's swap loops terminate only for even n; odd n gets the intended full reversal)
+    std::vector<uint64_t> Bt(n, 0);          // Bt[i] bit k = B'(i, k), y_i = parity(Bt[i] & x)
+    for (int i = 0; i < n; ++i)
+        for (int k = 0; k < n; ++k)
+            if (B[off + (n - 1 - i)][off + (n - 1 - k)]) Bt[i] |= 1ull << k;
+    // Gauss-Jordan inverse over GF(2)
+    std::vector<uint64_t> inv(n);
+    for (int i = 0; i < n; ++i) inv[i] = 1ull << i;
+    for (int c = 0; c < n; ++c) {
+        int p = -1;
+        for (int r = c; r < n; ++r) if ((Bt[r] >> c) & 1) { p = r; break; }
+        if (p < 0) { err = "BK matrix is singular"; return false; }
+        std::swap(Bt[c], Bt[p]);
+        std::swap(inv[c], inv[p]);
+        for (int r = 0; r < n; ++r)
+            if (r != c && ((Bt[r] >> c) & 1)) { Bt[r] ^= Bt[c]; inv[r] ^= inv[c]; }
+    }
+    rows = inv;                              // x_i = parity(inv[i] & y)
+    return true;
+}
+
+
 }  // namespace b200vqe

@@ -91,4 +91,7 @@ struct Rotation { uint64_t x, z; double imag_coeff; int param; };
 bool uccsd_rotations(int n_qubits, int n_electrons, const std::string &transformation,
                      std::vector<Rotation> &rot, int &n_params, std::string &err);
 
+// task/tasks/DiagonalizeTask.cpp:54-144: rows[i] such that occupation bit i of basis index j is parity(rows[i] & j)
+bool number_sector_rows(int n, const std::string &transformation, std::vector<uint64_t> &rows, std::string &err);
+
 }  // namespace b200vqe

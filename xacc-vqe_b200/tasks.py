@@ -232,15 +232,23 @@ class DiagonalizeTask:
     name = "vqe-diagonalize"
 
     def __init__(self, program: VQEProgram, buffer: Optional[AcceleratorBuffer] = None, tol: float = 1e-12, max_iter: int = 4000,
-                 seed: int = 1, want_vector: bool = False):
+                 seed: int = 1, want_vector: bool = False, n_electrons: Optional[int] = None, transformation: str = "jw"):
         self.program, self.buffer = program, buffer
+        # options "diag-number-symmetry" + "n-electrons" + "fermion-transformation" (DiagonalizeTask.cpp:48-57)
+        self.n_electrons, self.transformation = n_electrons, transformation
         self.tol, self.max_iter, self.seed, self.want_vector = tol, max_iter, seed, want_vector
         self.ground_state: Optional[np.ndarray] = None
         self.iterations, self.residual = 0, 0.0
 
     def execute(self, parameters: Sequence[float] = ()) -> VQETaskResult:
         be = self.program.backend
-        e0, it, res = be.lanczos_ground(tol=self.tol, max_iter=self.max_iter, want_vector=self.want_vector, seed=self.seed)
+        if self.n_electrons is not None:
+            be.set_number_sector(int(self.n_electrons), self.transformation)
+        try:
+            e0, it, res = be.lanczos_ground(tol=self.tol, max_iter=self.max_iter, want_vector=self.want_vector, seed=self.seed)
+        finally:
+            if self.n_electrons is not None:
+                be.set_number_sector(-1)
         self.iterations, self.residual = it, res
         if self.want_vector:
             # element order of the reference's eigenvector (DiagonalizeTask.cpp:189-193, :222-225)
@@ -333,7 +341,7 @@ TASKS = {"vqe-diagonalize": DiagonalizeTask, "compute-energy": ComputeEnergyVQET
 
 def execute(op, buffer: Optional[AcceleratorBuffer] = None, **kwargs) -> VQETaskResult:
     """xaccvqe.execute(op, buffer, **kwargs) (python/xacc-vqe-py.cpp:140-262).  Keys honoured: task, ansatz ('uccsd' or an
-    Ansatz/GateAnsatz object), n-qubits, n-electrons, vqe-params, transformation, diagonalize-backend, vqe-energy-delta,
+    Ansatz/GateAnsatz object), n-qubits, n-electrons, vqe-params, transformation, diagonalize-backend, diag-number-symmetry, fermion-transformation, vqe-energy-delta,
     vqe-iterations, vqe-persist-data, device.  'accelerator' and 'mpi-provider' are accepted and ignored: the accelerator is
     the B200 statevector backend, the communicator is NCCL inside a sharded handle."""
     kw = {k.replace("_", "-"): v for k, v in kwargs.items()}
@@ -358,7 +366,10 @@ def execute(op, buffer: Optional[AcceleratorBuffer] = None, **kwargs) -> VQETask
         buffer.n_qubits = n_qubits
     params = generate_parameters(program.getNParameters(), kw.get("vqe-params"), kw.get("seed"))
     if task == "vqe-diagonalize":
-        t = DiagonalizeTask(program, buffer, want_vector=bool(kw.get("print-ground-state", False)))
+        sym = bool(kw.get("diag-number-symmetry", False)) and "n-electrons" in kw        # both options, as DiagonalizeTask.cpp:54-55
+        t = DiagonalizeTask(program, buffer, want_vector=bool(kw.get("print-ground-state", False)),
+                            n_electrons=int(kw["n-electrons"]) if sym else None,
+                            transformation=str(kw.get("fermion-transformation", kw.get("transformation", "jw"))))
     elif task == "compute-energy":
         t = ComputeEnergyVQETask(program, buffer, persist_file=str(kw.get("vqe-persist-data", "")))
     else:
