@@ -310,7 +310,7 @@ def run_gpu(args):
                 traffic_tile = tj["k_tile_expect"]["dram_bytes_per_launch"]
         except Exception:
             traffic = None
-    tile = args.engine == "tile" if apply_op else args.engine != "stream"
+    tile = args.engine != "stream"
     if tile and traffic_tile is not None:
         traffic = traffic_tile
     roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,

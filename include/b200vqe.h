@@ -117,6 +117,11 @@ int b200vqe_debug_tile_plan(int n_qubits, int chunk_bits, int64_t n_terms, const
                             const double *coef_re, const double *coef_im, int64_t *n_batches, int64_t *n_groups,
                             int64_t *n_plan_terms, void *batches, void *groups, void *terms);
 
+/* Host-only: the TileRec[32 B] records (csrc/tile_plan.hpp) the <psi|H|psi> kernel walks for that plan; the r_begin / r_end
+ * fields of a TileBatch index them.  Call with NULL for the count. */
+int b200vqe_debug_tile_records(int n_qubits, int chunk_bits, int64_t n_terms, const uint64_t *xmask, const uint64_t *zmask,
+                               const double *coef_re, const double *coef_im, int64_t *n_records, void *records);
+
 /* Host-only: slab and tile-engine share of `rank` in a register sharded over `world` ranks (what
  * b200vqe_create_sharded / b200vqe_expectation use).  No device needed. */
 int b200vqe_debug_shard_layout(int n_qubits, int rank, int world, uint64_t *n_local, uint64_t *first_index,

@@ -12,9 +12,27 @@ import xaccvqe_b200 as xb
 
 TILE_BITS = 12
 BATCH_DT = np.dtype([("basis", "<u4", 10), ("seg", "<u4", 11), ("g_begin", "<i4"), ("g_end", "<i4"),
-                     ("t_begin", "<i4"), ("t_end", "<i4"), ("cls_end", "<i4", 5), ("pad1", "<i4", 2)])
+                     ("t_begin", "<i4"), ("t_end", "<i4"), ("cls_end", "<i4", 5), ("r_begin", "<i4"), ("r_end", "<i4")])
 GROUP_DT = np.dtype([("kb", "<u4"), ("n_even", "<u4"), ("n_odd", "<u4"), ("xv", "<u2"), ("hsel", "<i2")])
 TERM_DT = np.dtype([("packed", "<u8"), ("u", "<f8")])
+REC_DT = np.dtype([("kb", "<u4"), ("count", "<u4"), ("xv", "<u2"), ("key", "u1"), ("pad0", "u1"), ("pad1", "<u4"),
+                   ("packed0", "<u8"), ("u0", "<f8")])
+STAGE_RECS, STAGE_TERMS = 128, 256          # capacities of one batch (kStageRecs / kStageTerms in csrc/tile_plan.hpp)
+
+
+def get_records(n, c, xm, zm, cf):
+    lib = xb.capi.lib()
+    xm = np.ascontiguousarray(xm, np.uint64)
+    zm = np.ascontiguousarray(zm, np.uint64)
+    cr, ci = np.ascontiguousarray(cf.real), np.ascontiguousarray(cf.imag)
+    nr = C.c_int64()
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)
+    args = (C.c_int(n), C.c_int(c), C.c_int64(len(xm)), vp(xm), vp(zm), vp(cr), vp(ci), C.byref(nr))
+    assert lib.b200vqe_debug_tile_records(*args, None) == 0
+    R = np.zeros(nr.value, REC_DT)
+    assert REC_DT.itemsize == 32
+    assert lib.b200vqe_debug_tile_records(*args, vp(R)) == 0
+    return R
 
 
 def get_plan(n, c, xm, zm, cf):
@@ -92,6 +110,52 @@ def replay(n, c, B, G, T, psi, tile_begin=0, tile_count=None):
     return total
 
 
+def replay_records(n, c, B, R, T, psi):
+    """What k_tile_expect computes from the TileRec records: per record, the key fixes WHICH (even / odd nY) and XR (the
+    register part of the flip mask); XR != 0 visits the 8 registers with bit HS = top bit of XR clear, XR == 0 visits all."""
+    M = TILE_BITS - c
+    v = np.arange(1 << TILE_BITS, dtype=np.uint64)
+    mu = v >> np.uint64(c)
+    lo = v & np.uint64((1 << c) - 1)
+    total = 0.0
+    for b in B:
+        recs = R[b["r_begin"]:b["r_end"]]
+        assert len(recs) <= STAGE_RECS and b["t_end"] - b["t_begin"] <= STAGE_TERMS
+        assert list(recs["key"]) == sorted(recs["key"]) and np.all(recs["pad0"] == 0)
+        combo = np.zeros(1 << TILE_BITS, np.uint64)
+        for i in range(M):
+            combo ^= np.where((mu >> np.uint64(i)) & np.uint64(1), np.uint64(b["basis"][i]), np.uint64(0)).astype(np.uint64)
+        for t in range(1 << (n - TILE_BITS)):
+            rep = 0
+            for i in range(11):
+                rep |= (t & int(b["seg"][i])) << i
+            j = ((np.uint64(rep) ^ combo) << np.uint64(c)) | lo
+            tile = psi[j.astype(np.int64)]
+            for rec in recs:
+                key, xv = int(rec["key"]), int(rec["xv"])
+                which, xr = key >> 4, ((key & 15) + 1) & 15
+                assert xr == xv >> 8 and rec["count"] >= 1
+                assert b["t_begin"] <= rec["kb"] and rec["kb"] + rec["count"] <= b["t_end"]
+                assert T[rec["kb"]]["packed"] == rec["packed0"] and T[rec["kb"]]["u"] == rec["u0"]
+                r = v >> np.uint64(8)
+                if xr:
+                    hs = xr.bit_length() - 1
+                    act = ((r >> np.uint64(hs)) & np.uint64(1)) == 0
+                else:
+                    act = np.ones(len(v), bool)
+                va = v[act]
+                a, bb = tile[va.astype(np.int64)], tile[(va ^ np.uint64(xv)).astype(np.int64)]
+                w = np.conj(bb) * a
+                f = np.zeros(len(va))
+                for k in range(int(rec["kb"]), int(rec["kb"] + rec["count"])):
+                    packed, u = int(T[k]["packed"]), float(T[k]["u"])
+                    p0 = (bin(rep & packed & 0xFFFFFFFF).count("1") & 1) ^ parity(va & np.uint64(0xFF) & np.uint64((packed >> 32) & 0xFF))
+                    sr = parity((va >> np.uint64(8)) & np.uint64((packed >> 40) & 0xF))
+                    f += (1.0 - 2.0 * (p0 ^ sr)) * u
+                total += float(np.sum(f * (w.real if which == 0 else w.imag)))
+    return total
+
+
 def random_hamiltonian(n, T, seed, weights=None):
     rng = np.random.default_rng(seed)
     pa = rng.integers(0, 4, size=(T, n)) if weights is None else rng.choice(4, size=(T, n), p=weights)
@@ -126,6 +190,30 @@ def test_plan_replay_matches_oracle(n, T, c, seed, weights):
     e = replay(n, c, B, G, Tt, psi)
     eo, _ = co.expect(n, xm, zm, cf, psi)
     assert abs(e - eo.real) < 1e-11 * np.abs(cf).sum()
+    er = replay_records(n, c, B, get_records(n, c, xm, zm, cf), Tt, psi)
+    assert abs(er - eo.real) < 1e-11 * np.abs(cf).sum()
+
+
+def test_batch_capacity_splits_large_groups_and_batches():
+    """A diagonal group with more terms than one batch stages (kStageTerms) is cut into several groups of the same x, and a
+    subspace holding more groups than kStageRecs / 2 is spread over several batches; the records still give <psi|H|psi>."""
+    n, c = 13, 3
+    rng = np.random.default_rng(11)
+    zs = rng.choice(np.arange(1, 1 << n), size=600, replace=False).astype(np.uint64)          # 600 Z-only strings: one x = 0 group
+    gens = [int(g) for g in rng.integers(1, 1 << 6, 200, dtype=np.uint64)]                     # flips within the low 6 bits
+    xs = np.array(sorted(set(gens)), np.uint64)
+    xm = np.concatenate([np.zeros(len(zs), np.uint64), xs])
+    zm = np.concatenate([zs, np.zeros(len(xs), np.uint64)])
+    cf = rng.normal(size=len(xm)).astype(complex)
+    psi = rng.normal(size=1 << n) + 1j * rng.normal(size=1 << n)
+    psi /= np.linalg.norm(psi)
+    B, G, Tt = get_plan(n, c, xm, zm, cf)
+    R = get_records(n, c, xm, zm, cf)
+    assert len(Tt) == len(xm) and len(G) > len(xs) + 1 and len(B) >= 3
+    assert max(int(b["t_end"] - b["t_begin"]) for b in B) <= STAGE_TERMS
+    eo, _ = co.expect(n, xm, zm, cf, psi)
+    assert abs(replay(n, c, B, G, Tt, psi) - eo.real) < 1e-11 * np.abs(cf).sum()
+    assert abs(replay_records(n, c, B, R, Tt, psi) - eo.real) < 1e-11 * np.abs(cf).sum()
 
 
 def test_plan_batches_many_groups_for_structured_masks():

@@ -38,12 +38,12 @@ struct DeviceHam {
     std::vector<int64_t> pt_idx; std::vector<uint64_t> pt_x, pt_z; std::vector<int> pt_ny;
     // tile engine (kernels_tile.cuh): batches of xmask groups evaluated per HBM read of the state
     int tile_C = 0, tile_M = 0, n_tile_batches = 0, n_tile_groups = 0;
-    TileBatch *tl_batches = nullptr; TileGroup *tl_groups = nullptr; TileTerm *tl_terms = nullptr;
+    TileBatch *tl_batches = nullptr; TileRec *tl_recs = nullptr; TileTerm *tl_terms = nullptr;
     // tile engine for H psi: one plan per x_rank class (which peer slab the partners live in), concatenated
     struct ApplyClass { int x_rank; int b_begin, b_end; };
     std::vector<ApplyClass> ta_classes;
     int ta_C = 0, ta_M = 0, n_ta_batches = 0;
-    TileBatch *ta_batches = nullptr; TileGroup *ta_groups = nullptr; TileTerm *ta_terms = nullptr;
+    TileBatch *ta_batches = nullptr; TileRec *ta_recs = nullptr; TileTerm *ta_terms = nullptr;
     // natural-layout plan for the shared-memory sweep kernel (registers of up to kTileBits qubits)
     bool has_sweep_plan = false;
     TileBatch *sw_batch = nullptr; TileGroup *sw_groups = nullptr; TileTerm *sw_terms = nullptr;
@@ -52,13 +52,13 @@ struct DeviceHam {
 
     void free_device() {
         cudaFree(gd_e); cudaFree(tz_e); cudaFree(tu_e); cudaFree(gd_a); cudaFree(tz_a); cudaFree(tv_a);
-        cudaFree(tl_batches); cudaFree(tl_groups); cudaFree(tl_terms);
-        cudaFree(ta_batches); cudaFree(ta_groups); cudaFree(ta_terms);
+        cudaFree(tl_batches); cudaFree(tl_recs); cudaFree(tl_terms);
+        cudaFree(ta_batches); cudaFree(ta_recs); cudaFree(ta_terms);
         cudaFree(sw_batch); cudaFree(sw_groups); cudaFree(sw_terms);
         sw_batch = nullptr; sw_groups = nullptr; sw_terms = nullptr;
-        ta_batches = nullptr; ta_groups = nullptr; ta_terms = nullptr;
+        ta_batches = nullptr; ta_recs = nullptr; ta_terms = nullptr;
         gd_e = gd_a = nullptr; tz_e = tz_a = nullptr; tu_e = tv_a = nullptr;
-        tl_batches = nullptr; tl_groups = nullptr; tl_terms = nullptr;
+        tl_batches = nullptr; tl_recs = nullptr; tl_terms = nullptr;
     }
 };
 

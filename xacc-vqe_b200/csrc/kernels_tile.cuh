@@ -15,10 +15,6 @@
 #include "kernels.cuh"
 #include "tile_plan.hpp"
 
-#ifndef B200VQE_APPLY_NR
-#define B200VQE_APPLY_NR 4      // registers of a thread handled per pass over a group's terms in k_tile_apply (4 or 8)
-#endif
-
 namespace b200vqe {
 
 __device__ __forceinline__ double flip_bit(double v, unsigned word, int r) {
@@ -52,6 +48,7 @@ __device__ __forceinline__ double pm_one_hi(unsigned hi_word, int bit) {   // bi
     return __hiloint2double((int)((m & 0x80000000u) | 0x3ff00000u), 0);
 }
 
+// ---- class-ordered group walk over global-memory tables (used by k_sweep_small, kernels_small.cuh) ----
 // One xmask group on the 8 registers r whose bit HS equals BV (the other element of each pair has the
 // bit flipped when the group's xv has register bit HS; groups without a register bit call this for
 // BV = 0 and BV = 1).  WHICH = 0: even-nY terms on Re w, 1: odd-nY terms on Im w.
@@ -107,6 +104,84 @@ __device__ __forceinline__ void tile_class(const double2 (&a)[16], const double2
     }
 }
 
+// ---- expectation engine, per record ----------------------------------------------------------------
+// A record is the even-nY (WHICH = 0, uses Re w) or odd-nY (WHICH = 1, uses Im w) terms of one xmask group,
+// w = conj(psi[j^x]) psi[j].  The record's key fixes WHICH and XR = xv >> 8 at COMPILE time (records of a batch are
+// sorted by key, one specialised loop per key), so the partner of register r is row r ^ XR of thread v0 ^ xt:
+// eight LDS.128 at immediate offsets from one per-record address.
+//   XR != 0: HS = top bit of XR; a thread visits its 8 registers with bit HS clear (each pair once, weight 2 in u).
+//   XR == 0: the partner sits in the same row; all 16 registers are visited (two halves of 8), weight 1.
+template <int XR> struct XrInfo { static constexpr int HS = XR >= 8 ? 3 : (XR >= 4 ? 2 : (XR >= 2 ? 1 : 0)); };
+
+// one term on the 8 products w[]: sign = thread constant (one POPC) x Walsh function of the visited registers
+template <int HS, int BV>
+__device__ __forceinline__ void tile_term(const double (&w)[8], unsigned long long packed, double u, unsigned v0, unsigned rep,
+                                          double &acc) {
+    const unsigned zl = (unsigned)packed;                     // z on the high index bits
+    const unsigned hw = (unsigned)(packed >> 32);             // bits 0..7: thread bits of zv, 8..11: register bits
+    // coset part and thread part share one POPC: parity(a) ^ parity(b) = parity(a ^ b)
+    unsigned par = (unsigned)__popc((rep & zl) ^ (v0 & hw & 0xffu));
+    if (BV) par += hw >> (8 + HS);
+    // free register bits: i-bit k <-> r-bit (k < HS ? k : k + 1)
+    const double s0 = pm_one_hi(hw, 8 + (0 < HS ? 0 : 1));
+    const double s1 = pm_one_hi(hw, 8 + (1 < HS ? 1 : 2));
+    const double s2 = pm_one_hi(hw, 8 + (2 < HS ? 2 : 3));
+    const double us = __hiloint2double(__double2hiint(u) ^ (int)(par << 31), __double2loint(u));
+    acc = fma(us, signed_sum8(w, s0, s1, s2), acc);
+}
+
+template <int WHICH, int XR, int BV>
+__device__ __forceinline__ void tile_rec_half(const double2 (&a)[16], const double2 *__restrict__ P, unsigned v0, unsigned rep,
+                                              const int4 ra, const int4 rb, const double2 *__restrict__ s_terms, double &acc) {
+    constexpr int HS = XR ? XrInfo<XR>::HS : 3;
+    double w[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int r = ((i >> HS) << (HS + 1)) | (BV << HS) | (i & ((1 << HS) - 1));
+        const double2 b = P[(r ^ XR) << 8];
+        w[i] = WHICH == 0 ? fma(b.x, a[r].x, b.y * a[r].y) : fma(b.x, a[r].y, -(b.y * a[r].x));
+    }
+    tile_term<HS, BV>(w, ((unsigned long long)(unsigned)rb.y << 32) | (unsigned)rb.x, __hiloint2double(rb.w, rb.z), v0, rep, acc);
+    const int count = ra.y;
+    if (count > 1) {
+        const double2 *tp = s_terms + ra.x;
+        double2 t = tp[1];
+#pragma unroll 1
+        for (int e = 1; e < count; ++e) {
+            const double2 c = t;
+            if (e + 1 < count) t = tp[e + 1];
+            tile_term<HS, BV>(w, (unsigned long long)__double_as_longlong(c.x), c.y, v0, rep, acc);
+        }
+    }
+}
+
+template <int K>
+__device__ __forceinline__ void tile_rec(const double2 (&a)[16], const double2 *__restrict__ tile, unsigned v0, unsigned rep,
+                                         const int4 ra, const int4 rb, const double2 *__restrict__ s_terms, double &acc) {
+    constexpr int WHICH = K >> 4;
+    constexpr int XR = ((K & 15) + 1) & 15;
+    const double2 *P = tile + ((v0 ^ (unsigned)ra.z) & 0xffu);         // row 0 of the partner thread
+    tile_rec_half<WHICH, XR, 0>(a, P, v0, rep, ra, rb, s_terms, acc);
+    if (XR == 0) tile_rec_half<WHICH, XR, 1>(a, P, v0, rep, ra, rb, s_terms, acc);
+}
+
+// all records of the batch, key by key: s_recs holds (n_r + 1) records as int4 pairs, the last one a sentinel (key 255)
+template <int K>
+__device__ __forceinline__ void tile_runs(const double2 (&a)[16], const double2 *__restrict__ tile, unsigned v0, unsigned rep,
+                                          const int4 *__restrict__ s_recs, const double2 *__restrict__ s_terms, int &gi, int4 &ra,
+                                          int4 &rb, double &acc) {
+    if constexpr (K < kTileRecKeys) {
+        while (((unsigned)ra.z >> 16) == (unsigned)K) {
+            const int4 ca = ra, cb = rb;
+            ++gi;
+            ra = s_recs[2 * gi];                                       // next record (or the sentinel)
+            rb = s_recs[2 * gi + 1];
+            tile_rec<K>(a, tile, v0, rep, ca, cb, s_terms, acc);
+        }
+        tile_runs<K + 1>(a, tile, v0, rep, s_recs, s_terms, gi, ra, rb, acc);
+    }
+}
+
 __device__ __forceinline__ unsigned tile_rep(const TileBatch &sb, unsigned t) {
     unsigned rep = 0;
 #pragma unroll
@@ -118,19 +193,16 @@ __device__ __forceinline__ void prefetch_l2(const void *p) {
     asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
 }
 
-constexpr int kStageGroups = 64;     // descriptor records staged in shared memory per batch
-constexpr int kStageTerms = 192;
-
-// MINB = resident CTAs per SM the register allocation is held to (2: 128 registers, 3: 80 with a few spills)
+// MINB = resident CTAs per SM the register allocation is held to (2: 128 registers, 3: 80 with spills)
 template <int MINB>
 __global__ void __launch_bounds__(kBlock, MINB)
 k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_bytes, const TileBatch *__restrict__ batches, int n_batches,
-              unsigned long long tile_begin, unsigned long long tile_count, const TileGroup *__restrict__ groups,
+              unsigned long long tile_begin, unsigned long long tile_count, const TileRec *__restrict__ recs,
               const TileTerm *__restrict__ terms, double *partials, unsigned *counter, double *out) {
     extern __shared__ __align__(16) unsigned char tile_raw[];
     double2 *tile = reinterpret_cast<double2 *>(tile_raw);
     __shared__ TileBatch sb;
-    __shared__ __align__(16) int4 s_groups[kStageGroups];
+    __shared__ __align__(16) int4 s_recs[2 * (kStageRecs + 1)];
     __shared__ __align__(16) double2 s_terms[kStageTerms];
     const unsigned v0 = threadIdx.x;
     const unsigned lo = v0 & ((1u << C) - 1u);
@@ -141,9 +213,6 @@ k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_byte
     unsigned pcA = 0;                    // combo of the two rows this thread prefetches for the next tile
     unsigned rep_next = 0;
     bool have_next = false;
-    const int4 *gp = nullptr;            // group records of the current batch, indexed from 0
-    const TileTerm *tp = nullptr;        // term records, indexed by (kb - kb0)
-    int n_g = 0, c0 = 0, c1 = 0, c2 = 0, c3 = 0;
     const unsigned long long total = (unsigned long long)n_batches * tile_count;
 
     for (unsigned long long w = blockIdx.x; w < total; w += gridDim.x) {
@@ -161,24 +230,19 @@ k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_byte
             // the 8 lanes sharing a 128-byte line split its 16 rows between them: this thread takes rows 2(lane & 7), +1
             pcA = Tc ^ ((v0 & 1u) ? rb1 : 0u) ^ ((v0 & 2u) ? rb2 : 0u) ^ ((v0 & 4u) ? rb3 : 0u);
             have_next = false;
-            n_g = sb.g_end - sb.g_begin;
-            c0 = sb.cls_end[0]; c1 = sb.cls_end[1]; c2 = sb.cls_end[2]; c3 = sb.cls_end[3];
-            const uint32_t kb0 = (uint32_t)sb.t_begin;
+            // stage the batch's records (term indices made relative) + a sentinel, and its terms; the planner keeps every
+            // batch within kStageRecs / kStageTerms
+            const int n_r = sb.r_end - sb.r_begin;
             const int n_t = sb.t_end - sb.t_begin;
-            const int4 *gsrc = reinterpret_cast<const int4 *>(groups) + sb.g_begin;
-            if (n_g <= kStageGroups && n_t <= kStageTerms) {
-                for (int i = threadIdx.x; i < n_g; i += kBlock) {
-                    int4 g = gsrc[i];
-                    g.x -= (int)kb0;
-                    s_groups[i] = g;
-                }
-                for (int i = threadIdx.x; i < n_t; i += kBlock) s_terms[i] = reinterpret_cast<const double2 *>(terms)[kb0 + i];
-                gp = s_groups;
-                tp = reinterpret_cast<const TileTerm *>(s_terms);
-            } else {
-                gp = gsrc;
-                tp = terms;
+            const int4 *rsrc = reinterpret_cast<const int4 *>(recs + sb.r_begin);
+            for (int i = threadIdx.x; i < 2 * n_r; i += kBlock) {
+                int4 q = rsrc[i];
+                if (!(i & 1)) q.x -= sb.t_begin;
+                s_recs[i] = q;
             }
+            if (threadIdx.x == 0) s_recs[2 * n_r] = make_int4(0, 0, 0xff << 16, 0);
+            const double2 *tsrc = reinterpret_cast<const double2 *>(terms) + sb.t_begin;
+            for (int i = threadIdx.x; i < n_t; i += kBlock) s_terms[i] = tsrc[i];
             __syncthreads();
         }
         const unsigned rep = have_next ? rep_next : tile_rep(sb, (unsigned)t);   // high index (j >> C) has at most 32 bits
@@ -203,11 +267,9 @@ k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_byte
                 prefetch_l2(psi_lo + (unsigned long long)(h0 ^ rb0) * chunk_bytes);
             }
         }
-        tile_class<0, false>(a, tile, v0, rep, gp, 0, c0, tp, acc);
-        tile_class<1, false>(a, tile, v0, rep, gp, c0, c1, tp, acc);
-        tile_class<2, false>(a, tile, v0, rep, gp, c1, c2, tp, acc);
-        tile_class<3, false>(a, tile, v0, rep, gp, c2, c3, tp, acc);
-        tile_class<3, true>(a, tile, v0, rep, gp, c3, n_g, tp, acc);   // no register bit in xv: every amplitude, weight 1
+        int gi = 0;
+        int4 ra = s_recs[0], rb = s_recs[1];
+        tile_runs<0>(a, tile, v0, rep, s_recs, s_terms, gi, ra, rb, acc);
     }
     double v[1] = {acc};
     grid_reduce<1>(v, partials, counter, out, 1.0);
@@ -225,60 +287,86 @@ k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_byte
 //   first != 0:  dst = in_scale * acc - prev_scale * dst   (prev_scale = 0 unless fuse_prev)   [Lanczos: w' = H v_j - beta_j v_{j-1}]
 //   first == 0:  dst += in_scale * acc
 // ---------------------------------------------------------------------------------------------
-template <int PART, int NR, int WHICH>      // registers [PART*NR, PART*NR + NR)
-__device__ __forceinline__ void apply_terms(double2 (&acc)[16], const double2 *__restrict__ tile, unsigned pidx, unsigned v0,
-                                            unsigned rep, uint32_t k, uint32_t count, const TileTerm *terms) {
-    TileTermRaw t = load_term(terms, k);
-    double2 b[NR];
-#pragma unroll
-    for (int i = 0; i < NR; ++i) b[i] = tile[pidx ^ ((unsigned)(PART * NR + i) << 8)];
-    double f[NR];
-#pragma unroll
-    for (int i = 0; i < NR; ++i) f[i] = 0.0;
-    for (uint32_t e = 0; e < count; ++e) {
-        const unsigned zl = (unsigned)t.packed;
-        const unsigned hw = (unsigned)(t.packed >> 32);
-        const double u = t.u;
-        if (e + 1 < count) t = load_term(terms, k + e + 1);
+// one record on the 16 outputs of a thread: partner of register r is row r ^ XR of thread v0 ^ xt (immediate offsets)
+template <int WHICH, int XR>
+__device__ __forceinline__ void apply_rec_body(double2 (&acc)[16], const double2 *__restrict__ P, unsigned v0, unsigned rep,
+                                               const int4 ra, const int4 rb, const double2 *__restrict__ s_terms) {
+    const int count = ra.y;
+    if (count == 1) {
+        // single term (every group of an unstructured Hamiltonian): the factor at register r is +-u
+        const unsigned zl = (unsigned)rb.x, hw = (unsigned)rb.y;
         const unsigned par = (unsigned)__popc((rep & zl) ^ (v0 & hw & 0xffu)) & 1u;
-        const unsigned S = (hw >> 16) ^ (0u - par);            // bit r: sign of this term at register r
+        const unsigned S = (hw >> 16) ^ (0u - par);            // bit r: sign of the term at register r
+        const double u = __hiloint2double(rb.w, rb.z);
 #pragma unroll
-        for (int i = 0; i < NR; ++i) f[i] += flip_bit(u, S, PART * NR + i);
+        for (int r = 0; r < 16; ++r) {
+            const double2 b = P[(r ^ XR) << 8];
+            const double f = flip_bit(u, S, r);
+            if (WHICH == 0) {            // even nY: real factor
+                acc[r].x = fma(f, b.x, acc[r].x);
+                acc[r].y = fma(f, b.y, acc[r].y);
+            } else {                     // odd nY: factor i * f
+                acc[r].x = fma(-f, b.y, acc[r].x);
+                acc[r].y = fma(f, b.x, acc[r].y);
+            }
+        }
+        return;
     }
+    const double2 *tp = s_terms + ra.x;
 #pragma unroll
-    for (int i = 0; i < NR; ++i) {
-        const int r = PART * NR + i;
-        if (WHICH == 0) {            // even nY: real factor
-            acc[r].x = fma(f[i], b[i].x, acc[r].x);
-            acc[r].y = fma(f[i], b[i].y, acc[r].y);
-        } else {                     // odd nY: factor i * f
-            acc[r].x = fma(-f[i], b[i].y, acc[r].x);
-            acc[r].y = fma(f[i], b[i].x, acc[r].y);
+    for (int part = 0; part < 4; ++part) {       // four registers at a time keeps the factor sums in registers
+        double f[4] = {0.0, 0.0, 0.0, 0.0};
+        double2 t = tp[0];
+#pragma unroll 1
+        for (int e = 0; e < count; ++e) {
+            const unsigned long long packed = (unsigned long long)__double_as_longlong(t.x);
+            const double u = t.y;
+            if (e + 1 < count) t = tp[e + 1];
+            const unsigned zl = (unsigned)packed, hw = (unsigned)(packed >> 32);
+            const unsigned par = (unsigned)__popc((rep & zl) ^ (v0 & hw & 0xffu)) & 1u;
+            const unsigned S = (hw >> 16) ^ (0u - par);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) f[i] += flip_bit(u, S, part * 4 + i);
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int r = part * 4 + i;
+            const double2 b = P[(r ^ XR) << 8];
+            if (WHICH == 0) {
+                acc[r].x = fma(f[i], b.x, acc[r].x);
+                acc[r].y = fma(f[i], b.y, acc[r].y);
+            } else {
+                acc[r].x = fma(-f[i], b.y, acc[r].x);
+                acc[r].y = fma(f[i], b.x, acc[r].y);
+            }
         }
     }
 }
 
-template <int WHICH>
-__device__ __forceinline__ void apply_pass(double2 (&acc)[16], const double2 *__restrict__ tile, unsigned pidx, unsigned v0,
-                                           unsigned rep, uint32_t k, uint32_t count, const TileTerm *terms) {
-    constexpr int NR = B200VQE_APPLY_NR;
-#pragma unroll
-    for (int part = 0; part < 16 / NR; ++part) {
-        if (part == 0) apply_terms<0, NR, WHICH>(acc, tile, pidx, v0, rep, k, count, terms);
-        if (part == 1) apply_terms<1 % (16 / NR), NR, WHICH>(acc, tile, pidx, v0, rep, k, count, terms);
-        if (part == 2) apply_terms<2 % (16 / NR), NR, WHICH>(acc, tile, pidx, v0, rep, k, count, terms);
-        if (part == 3) apply_terms<3 % (16 / NR), NR, WHICH>(acc, tile, pidx, v0, rep, k, count, terms);
+template <int K>
+__device__ __forceinline__ void apply_runs(double2 (&acc)[16], const double2 *__restrict__ tile, unsigned v0, unsigned rep,
+                                           const int4 *__restrict__ s_recs, const double2 *__restrict__ s_terms, int &gi, int4 &ra,
+                                           int4 &rb) {
+    if constexpr (K < kTileRecKeys) {
+        while (((unsigned)ra.z >> 16) == (unsigned)K) {
+            const int4 ca = ra, cb = rb;
+            ++gi;
+            ra = s_recs[2 * gi];
+            rb = s_recs[2 * gi + 1];
+            apply_rec_body<(K >> 4), (((K & 15) + 1) & 15)>(acc, tile + ((v0 ^ (unsigned)ca.z) & 0xffu), v0, rep, ca, cb, s_terms);
+        }
+        apply_runs<K + 1>(acc, tile, v0, rep, s_recs, s_terms, gi, ra, rb);
     }
 }
 
 __global__ void __launch_bounds__(kBlock, 2)
 k_tile_apply(const double2 *__restrict__ src, double2 *__restrict__ dst, int C, int M, unsigned chunk_bytes,
-             const TileBatch *__restrict__ batch, unsigned tile_count, const TileGroup *__restrict__ groups,
+             const TileBatch *__restrict__ batch, unsigned tile_count, const TileRec *__restrict__ recs,
              const TileTerm *__restrict__ terms, int first, const double *norm_src, const double *norm_prev, int fuse_prev) {
     extern __shared__ __align__(16) unsigned char tile_raw[];
     double2 *tile = reinterpret_cast<double2 *>(tile_raw);
     __shared__ TileBatch sb;
-    __shared__ __align__(16) int4 s_groups[kStageGroups];
+    __shared__ __align__(16) int4 s_recs[2 * (kStageRecs + 1)];
     __shared__ __align__(16) double2 s_terms[kStageTerms];
     const unsigned v0 = threadIdx.x;
     const unsigned lo = v0 & ((1u << C) - 1u);
@@ -287,26 +375,27 @@ k_tile_apply(const double2 *__restrict__ src, double2 *__restrict__ dst, int C, 
     unsigned Tc = 0;
     for (int i = 0; i < 8 - C; ++i) if ((v0 >> (C + i)) & 1u) Tc ^= sb.basis[i];
     const unsigned rb0 = sb.basis[M - 4], rb1 = sb.basis[M - 3], rb2 = sb.basis[M - 2], rb3 = sb.basis[M - 1];
-    const int n_g = sb.g_end - sb.g_begin;
-    const uint32_t kb0 = (uint32_t)sb.t_begin;
-    const int n_t = sb.t_end - sb.t_begin;
-    const int4 *gp = reinterpret_cast<const int4 *>(groups) + sb.g_begin;
-    const TileTerm *tp = terms;
-    if (n_g <= kStageGroups && n_t <= kStageTerms) {
-        for (int i = threadIdx.x; i < n_g; i += kBlock) {
-            int4 g = gp[i];
-            g.x -= (int)kb0;
-            s_groups[i] = g;
+    // the 8 lanes sharing a 128-byte line split its 16 rows between them: this thread prefetches rows 2(lane & 7), +1
+    const unsigned pcA = Tc ^ ((v0 & 1u) ? rb1 : 0u) ^ ((v0 & 2u) ? rb2 : 0u) ^ ((v0 & 4u) ? rb3 : 0u);
+    {   // stage the batch's records (+ sentinel) and terms; the planner keeps every batch within kStageRecs / kStageTerms
+        const int n_r = sb.r_end - sb.r_begin;
+        const int n_t = sb.t_end - sb.t_begin;
+        const int4 *rsrc = reinterpret_cast<const int4 *>(recs + sb.r_begin);
+        for (int i = threadIdx.x; i < 2 * n_r; i += kBlock) {
+            int4 q = rsrc[i];
+            if (!(i & 1)) q.x -= sb.t_begin;
+            s_recs[i] = q;
         }
-        for (int i = threadIdx.x; i < n_t; i += kBlock) s_terms[i] = reinterpret_cast<const double2 *>(terms)[kb0 + i];
-        gp = s_groups;
-        tp = reinterpret_cast<const TileTerm *>(s_terms);
+        if (threadIdx.x == 0) s_recs[2 * n_r] = make_int4(0, 0, 0xff << 16, 0);
+        const double2 *tsrc = reinterpret_cast<const double2 *>(terms) + sb.t_begin;
+        for (int i = threadIdx.x; i < n_t; i += kBlock) s_terms[i] = tsrc[i];
     }
     __syncthreads();
     const double in_scale = norm_src ? 1.0 / *norm_src : 1.0;
     const double prev_scale = fuse_prev ? (*norm_src) / (*norm_prev) : 0.0;
     const char *src_lo = reinterpret_cast<const char *>(src + lo);
     char *dst_lo = reinterpret_cast<char *>(dst + lo);
+    const bool reads_dst = !first || fuse_prev;
 
     for (unsigned t = blockIdx.x; t < tile_count; t += gridDim.x) {
         const unsigned rep = tile_rep(sb, t);
@@ -323,18 +412,25 @@ k_tile_apply(const double2 *__restrict__ src, double2 *__restrict__ dst, int C, 
             for (int r = 0; r < 16; ++r) tile[((unsigned)r << 8) | v0] = a[r];
         }
         __syncthreads();
+        {   // pull this tile's dst lines and the CTA's next src tile into L2 while the records are being walked
+            const unsigned h0 = rep ^ pcA;
+            if (reads_dst) {
+                prefetch_l2(dst_lo + (unsigned long long)h0 * chunk_bytes);
+                prefetch_l2(dst_lo + (unsigned long long)(h0 ^ rb0) * chunk_bytes);
+            }
+            if (t + gridDim.x < tile_count) {
+                const unsigned h1 = tile_rep(sb, t + gridDim.x) ^ pcA;
+                prefetch_l2(src_lo + (unsigned long long)h1 * chunk_bytes);
+                prefetch_l2(src_lo + (unsigned long long)(h1 ^ rb0) * chunk_bytes);
+            }
+        }
         double2 acc[16];
 #pragma unroll
         for (int r = 0; r < 16; ++r) acc[r] = make_double2(0.0, 0.0);
-        if (n_g) {
-            int4 g = gp[0];
-            for (int gi = 0; gi < n_g; ++gi) {
-                const int4 gc = g;
-                if (gi + 1 < n_g) g = gp[gi + 1];
-                const unsigned pidx = ((unsigned)gc.w ^ v0) & 0xfffu;
-                if (gc.y) apply_pass<0>(acc, tile, pidx, v0, rep, (uint32_t)gc.x, (uint32_t)gc.y, tp);
-                if (gc.z) apply_pass<1>(acc, tile, pidx, v0, rep, (uint32_t)(gc.x + gc.y), (uint32_t)gc.z, tp);
-            }
+        {
+            int gi = 0;
+            int4 ra = s_recs[0], rb = s_recs[1];
+            apply_runs<0>(acc, tile, v0, rep, s_recs, s_terms, gi, ra, rb);
         }
 #pragma unroll
         for (int r = 0; r < 16; ++r) {
@@ -352,7 +448,7 @@ k_tile_apply(const double2 *__restrict__ src, double2 *__restrict__ dst, int C, 
                 o.x += q.x;
                 o.y += q.y;
             }
-            *p = o;
+            __stcs(p, o);
         }
     }
 }

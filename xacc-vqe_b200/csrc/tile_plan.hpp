@@ -34,7 +34,7 @@ struct TileBatch {                   // 128 bytes
     int32_t g_begin, g_end;          // groups of this batch
     int32_t t_begin, t_end;          // terms of this batch
     int32_t cls_end[kTileClasses];   // end of each hsel class, relative to g_begin
-    int32_t pad1[2];
+    int32_t r_begin, r_end;          // TileRec range of this batch (expectation engine; see build_tile_records)
 };
 static_assert(sizeof(TileBatch) == 128, "TileBatch layout");
 
@@ -54,6 +54,26 @@ struct TileTerm {                    // 16 bytes
 };
 static_assert(sizeof(TileTerm) == 16, "TileTerm layout");
 
+// One record of the expectation kernel: the even-nY or the odd-nY terms of one xmask group, first term inline.
+// Records of a batch are sorted by key, so the device runs one straight-line, fully specialised loop per key:
+//   key = which * 16 + (xr ? xr - 1 : 15),  xr = xv >> 8 (register bits of the virtual flip mask), which = 0 even nY / 1 odd nY
+struct TileRec {                     // 32 bytes
+    uint32_t kb;                     // first term (relative to the batch's t_begin once staged)
+    uint32_t count;                  // terms of this record (>= 1)
+    uint16_t xv;
+    uint8_t key;
+    uint8_t pad0;
+    uint32_t pad1;
+    uint64_t packed0;                // terms[kb].packed
+    double u0;                       // terms[kb].u
+};
+static_assert(sizeof(TileRec) == 32, "TileRec layout");
+
+constexpr int kTileRecKeys = 32;
+constexpr int kStageRecs = 128;      // records / terms of one batch staged in shared memory by k_tile_expect;
+constexpr int kStageTerms = 256;     // expectation plans are built with these as per-batch capacities
+constexpr int kStageGroupsCap = kStageRecs / 2;
+
 struct TilePlanTermIn { uint64_t x, z; double u; int odd; int64_t idx; };
 
 struct TilePlan {
@@ -62,6 +82,7 @@ struct TilePlan {
     std::vector<TileGroup> groups;
     std::vector<TileTerm> terms;
     std::vector<int64_t> term_src;   // plan term -> index into the input array
+    std::vector<TileRec> recs;       // expectation engine only (build_tile_records)
 };
 
 // Which tiles (cosets) of every batch a rank of a sharded register evaluates in <psi|H|psi>: a contiguous 1/world share;
@@ -113,7 +134,10 @@ inline uint16_t sign_word16(unsigned zr) {   // bit r = parity(r & zr), r = 0..1
 // pair_weights: expectation plans double the coefficients of groups evaluated once per pair; apply plans do not.
 // natural (n == kTileBits only): one batch whose virtual index equals the amplitude index (basis = unit vectors in order),
 // for kernels that keep the whole register in shared memory in its natural order (k_sweep_small).
-inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> &in, bool pair_weights = true, bool natural = false) {
+// max_groups / max_terms (0 = unlimited): capacity of one batch; an xmask group with more terms than max_terms is cut
+// into several groups of the same x.
+inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> &in, bool pair_weights = true, bool natural = false,
+                                size_t max_groups = 0, size_t max_terms = 0) {
     using namespace tileplan;
     TilePlan P;
     P.n = n; P.C = C; P.M = kTileBits - C;
@@ -133,7 +157,7 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
     std::vector<G> gs;
     for (size_t i = 0; i < order.size();) {
         size_t j = i;
-        while (j < order.size() && in[order[j]].x == in[order[i]].x) ++j;
+        while (j < order.size() && in[order[j]].x == in[order[i]].x && (!max_terms || j - i < max_terms)) ++j;
         gs.push_back(G{in[order[i]].x, i, j});
         i = j;
     }
@@ -174,6 +198,15 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
                 for (size_t g : it->second) if (!done[g]) members.push_back(g);
             }
             std::sort(members.begin(), members.end());
+        }
+        if (max_groups || max_terms) {             // batch capacity: the rest stays unassigned for later batches
+            size_t keep = 0, nt = 0;
+            for (; keep < members.size(); ++keep) {
+                const size_t t = gs[members[keep]].te - gs[members[keep]].tb;
+                if ((max_groups && keep >= max_groups) || (max_terms && nt + t > max_terms)) break;
+                nt += t;
+            }
+            members.resize(keep);
         }
         // ---- order the basis: the kTileRegBits coordinates that cover most work go on the register bits ----
         const int dim = (int)rr.b.size();
@@ -272,6 +305,34 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
         P.batches.push_back(B);
     }
     return P;
+}
+
+// Records of the expectation kernel for a plan built with pair_weights = true and the kStage* capacities.
+inline void build_tile_records(TilePlan &P) {
+    P.recs.clear();
+    for (TileBatch &B : P.batches) {
+        std::vector<TileRec> rs;
+        for (int g = B.g_begin; g < B.g_end; ++g) {
+            const TileGroup &tg = P.groups[g];
+            const unsigned xr = tg.xv >> (kTileBits - kTileRegBits);
+            for (int which = 0; which < 2; ++which) {
+                const uint32_t cnt = which ? tg.n_odd : tg.n_even;
+                if (!cnt) continue;
+                TileRec r{};
+                r.kb = tg.kb + (which ? tg.n_even : 0);
+                r.count = cnt;
+                r.xv = tg.xv;
+                r.key = (uint8_t)(which * 16 + (xr ? xr - 1 : 15));
+                r.packed0 = P.terms[r.kb].packed;
+                r.u0 = P.terms[r.kb].u;
+                rs.push_back(r);
+            }
+        }
+        std::stable_sort(rs.begin(), rs.end(), [](const TileRec &a, const TileRec &b) { return a.key < b.key; });
+        B.r_begin = (int32_t)P.recs.size();
+        P.recs.insert(P.recs.end(), rs.begin(), rs.end());
+        B.r_end = (int32_t)P.recs.size();
+    }
 }
 
 }  // namespace b200vqe
