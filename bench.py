@@ -165,7 +165,7 @@ def run_reference(args):
                        "n_qubits": n, "n_terms": int(len(xm))},
             "cpu_baseline": base,
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit(line)
 
 
 def run_gpu(args):
@@ -198,6 +198,7 @@ def run_gpu(args):
     be.set_option("expect-engine", args.engine)
     be.set_option("apply-engine", args.engine)
     be.set_option("tile-chunk-bits", args.chunk_bits)
+    be.set_option("tile-bits", args.tile_bits)
     be.set_option("tile-ctas-per-sm", args.tile_ctas)
     be.set_hamiltonian(xm, zm, cf)
     Tn, G = be.hamiltonian_stats()
@@ -314,7 +315,7 @@ def run_gpu(args):
     if tile and traffic_tile is not None:
         traffic = traffic_tile
     roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-            "kernel": ("k_tile_apply" if tile else "k_apply<8,true>") if apply_op else ("k_tile_expect<2>" if tile else "k_expect_energy<8,true>"),
+            "kernel": ("k_tile_apply" if tile else "k_apply<8,true>") if apply_op else (("k_tile_expect_db<3>" if args.tile_bits == 11 else "k_tile_expect<2>") if tile else "k_expect_energy<8,true>"),
             "peak_source": peak_src,
             "launches_per_step": int(launches // max(1, args.steps)),
             "note": ("achieved = ALGORITHMIC bytes 16 B x 2^n_local x G (SURVEY.md 8d) / CUDA-event time of the step's single "
@@ -337,14 +338,35 @@ def run_gpu(args):
     if world == 1 and not args.no_cpu:
         base, _, _ = cpu_baseline(n, xm, zm, cf, args.cpu_terms)
         line["cpu_baseline"] = base
-    print(json.dumps(line))
-    sys.stdout.flush()
+    emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def _guard_stdout():
+    """stdout carries exactly ONE JSON line: everything libraries print (NCCL's version banner, torch warnings) goes to
+    stderr; emit() writes the line to the saved descriptor."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line: dict):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    _guard_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
@@ -357,6 +379,7 @@ def main():
     ap.add_argument("--op", default="expect", choices=["expect", "apply"], help="expect: <psi|H|psi> (headline); apply: dst = H psi")
     ap.add_argument("--engine", default="auto", choices=["auto", "tile", "stream"], help="<psi|H|psi> kernel family")
     ap.add_argument("--tile-ctas", type=int, default=2, choices=[2, 3], help="tile engine: resident CTAs per SM")
+    ap.add_argument("--tile-bits", type=int, default=12, choices=[11, 12], help="tile engine: 12 = 4096-amplitude tiles, 11 = 2048 double-buffered")
     ap.add_argument("--chunk-bits", type=int, default=3, help="tile engine: log2 contiguous amplitudes per HBM chunk")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -97,6 +97,8 @@ const char *b200vqe_last_error(b200vqe_handle h);
 /* String options in the manner of xacc::setOption(key, value) (e.g. task/tasks/DiagonalizeTask.cpp:15-30).
  *   "expect-engine"   = "auto" | "tile" | "stream"   which <psi|H|psi> kernel set_hamiltonian prepares
  *   "apply-engine"    = "auto" | "tile" | "stream"   the same for H psi (b200vqe_apply_h, b200vqe_lanczos_ground)
+ *   "tile-bits"       = "12" | "11"                  tile of the <psi|H|psi> engine: 4096 amplitudes single-buffered (two CTAs
+ *                                                    per SM) | 2048 amplitudes double-buffered with cp.async (three CTAs per SM)
  *   "tile-ctas-per-sm" = "2" | "3"                   resident CTAs per SM of the tile engine's <psi|H|psi> kernel
  *   "tile-chunk-bits" = "2".."8"                     contiguous amplitudes per HBM chunk of the tile engine
  * Options take effect at the next b200vqe_set_hamiltonian. */
@@ -113,18 +115,18 @@ int b200vqe_hamiltonian_stats(b200vqe_handle h, int64_t *n_terms, int64_t *n_gro
 
 /* Host-only view of the tile-engine plan (see csrc/tile_plan.hpp) for a Hermitian term list: raw
  * TileBatch[128 B], TileGroup[16 B], TileTerm[16 B] records.  Call with NULL arrays for the counts. */
-int b200vqe_debug_tile_plan(int n_qubits, int chunk_bits, int64_t n_terms, const uint64_t *xmask, const uint64_t *zmask,
+int b200vqe_debug_tile_plan(int n_qubits, int chunk_bits, int tile_bits /* 12 | 11 */, int64_t n_terms, const uint64_t *xmask, const uint64_t *zmask,
                             const double *coef_re, const double *coef_im, int64_t *n_batches, int64_t *n_groups,
                             int64_t *n_plan_terms, void *batches, void *groups, void *terms);
 
 /* Host-only: the TileRec[32 B] records (csrc/tile_plan.hpp) the <psi|H|psi> kernel walks for that plan; the r_begin / r_end
  * fields of a TileBatch index them.  Call with NULL for the count. */
-int b200vqe_debug_tile_records(int n_qubits, int chunk_bits, int64_t n_terms, const uint64_t *xmask, const uint64_t *zmask,
+int b200vqe_debug_tile_records(int n_qubits, int chunk_bits, int tile_bits, int64_t n_terms, const uint64_t *xmask, const uint64_t *zmask,
                                const double *coef_re, const double *coef_im, int64_t *n_records, void *records);
 
 /* Host-only: slab and tile-engine share of `rank` in a register sharded over `world` ranks (what
  * b200vqe_create_sharded / b200vqe_expectation use).  No device needed. */
-int b200vqe_debug_shard_layout(int n_qubits, int rank, int world, uint64_t *n_local, uint64_t *first_index,
+int b200vqe_debug_shard_layout(int n_qubits, int rank, int world, int tile_bits, uint64_t *n_local, uint64_t *first_index,
                                uint64_t *tile_begin, uint64_t *tile_count);
 
 /* State */

@@ -106,16 +106,47 @@ def test_tile_engine_matches_streaming_kernel_and_oracle(xb, n, T, seed, cbits):
     eo, _ = co.expect(n, xm, zm, cf, psi)
     scale = np.abs(cf).sum()
     got = {}
-    for engine in ("tile", "stream"):
+    for engine, tile_bits in (("tile", 12), ("tile", 11), ("stream", 12)):
         be = xb.Backend(n)
         be.set_option("expect-engine", engine)
         be.set_option("tile-chunk-bits", cbits)
+        be.set_option("tile-bits", tile_bits)       # 12: single-buffer kernel, 11: double-buffered cp.async kernel
         be.set_hamiltonian(xm, zm, cf)
         be.upload(psi)
-        got[engine] = be.expectation()
-        assert abs(got[engine] - eo) < REL * scale, engine
+        got[engine, tile_bits] = be.expectation()
+        assert abs(got[engine, tile_bits] - eo) < REL * scale, (engine, tile_bits)
+        assert abs(be.expectation() - got[engine, tile_bits]) == 0.0      # deterministic reduction order
         be.close()
-    assert abs(got["tile"] - got["stream"]) < REL * scale
+    assert abs(got["tile", 12] - got["stream", 12]) < REL * scale
+    assert abs(got["tile", 11] - got["stream", 12]) < REL * scale
+
+
+def test_tile_engine_many_terms_per_group(xb):
+    """Structured operator: few flip masks, many Z patterns per mask (multi-term records, batch capacity splits)."""
+    n = 14
+    rng = np.random.default_rng(77)
+    xs = rng.integers(0, 1 << 6, size=900, dtype=np.uint64) << np.uint64(3)
+    zs = rng.integers(0, 1 << n, size=900, dtype=np.uint64)
+    keys = sorted({(int(x), int(z)) for x, z in zip(xs, zs) if x or z})
+    xm = np.array([k[0] for k in keys], np.uint64)
+    zm = np.array([k[1] for k in keys], np.uint64)
+    ny = np.array([bin(int(x) & int(z)).count("1") for x, z in zip(xm, zm)])
+    cf = rng.normal(size=len(xm)) * (1j ** (ny % 4))
+    psi = random_state(n, 78)
+    eo, _ = co.expect(n, xm, zm, cf, psi)
+    for tile_bits in (12, 11):
+        be = xb.Backend(n)
+        be.set_option("expect-engine", "tile")
+        be.set_option("tile-bits", tile_bits)
+        be.set_hamiltonian(xm, zm, cf)
+        be.upload(psi)
+        assert abs(be.expectation() - eo) < REL * np.abs(cf).sum(), tile_bits
+        be.n_slots(2)
+        be.set_option("apply-engine", "tile")
+        be.set_hamiltonian(xm, zm, cf)
+        be.apply_h(0, 1)
+        assert np.abs(be.download(1) - co.apply(n, xm, zm, cf, psi)).max() < 1e-12 * np.abs(cf).sum()
+        be.close()
 
 
 @pytest.mark.parametrize("n,T,seed,cbits", [(12, 30, 41, 3), (15, 200, 42, 2), (18, 64, 43, 3), (20, 48, 44, 5), (21, 20, 45, 8)])

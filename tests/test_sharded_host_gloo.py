@@ -12,9 +12,9 @@ import pytest
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _layout(lib, n, rank, world):
+def _layout(lib, n, rank, world, tile_bits=12):
     nl, first, tb, tc = C.c_uint64(), C.c_uint64(), C.c_uint64(), C.c_uint64()
-    rc = lib.b200vqe_debug_shard_layout(C.c_int(n), C.c_int(rank), C.c_int(world), C.byref(nl), C.byref(first), C.byref(tb), C.byref(tc))
+    rc = lib.b200vqe_debug_shard_layout(C.c_int(n), C.c_int(rank), C.c_int(world), C.c_int(tile_bits), C.byref(nl), C.byref(first), C.byref(tb), C.byref(tc))
     assert rc == 0
     return nl.value, first.value, tb.value, tc.value
 
@@ -49,6 +49,13 @@ def _worker(rank, world, port, n, T, seed, q):
     part = tp.replay(n, 3, B, G, Tt, psi, tile_begin=tb, tile_count=tc)
     tot = torch.tensor([part], dtype=torch.float64)
     dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    # the same with the 2048-amplitude tiles / per-key records of the double-buffered kernel
+    _, _, tb11, tc11 = _layout(lib, n, rank, world, tile_bits=11)
+    B11, _, T11 = tp.get_plan(n, 3, xm, zm, cf, tb=11)
+    part11 = tp.replay_records(n, 3, B11, tp.get_records(n, 3, xm, zm, cf, tb=11), T11, psi, tb=11, tile_begin=tb11, tile_count=tc11)
+    tot11 = torch.tensor([part11], dtype=torch.float64)
+    dist.all_reduce(tot11, op=dist.ReduceOp.SUM)
+    assert abs(tot11.item() - tot.item()) < 1e-11 * float(np.abs(cf).sum())
     # norm^2 of the sharded state: local slab sums, all-reduced (b200vqe_state_norm2 on a sharded handle)
     nrm = torch.tensor([float(np.vdot(psi[first:first + nloc], psi[first:first + nloc]).real)], dtype=torch.float64)
     dist.all_reduce(nrm, op=dist.ReduceOp.SUM)
@@ -94,20 +101,20 @@ def test_two_rank_expectation_decomposition(n, T, seed):
 def test_shard_layout_covers_every_tile_once():
     import xaccvqe_b200 as xb
     lib = xb.capi.lib()
-    for n in (12, 13, 14, 20, 31, 32):
+    for n, tile_bits in [(n, t) for n in (12, 13, 14, 20, 31, 32) for t in (12, 11)]:
         for world in (1, 2, 4, 8):
             if n - int(np.log2(world)) < 1:
                 continue
             spans, slabs = [], []
             for r in range(world):
-                nloc, first, tb, tc = _layout(lib, n, r, world)
+                nloc, first, tb, tc = _layout(lib, n, r, world, tile_bits)
                 slabs.append((first, nloc))
                 if tc:
                     spans.append((tb, tc))
             assert sum(c for _, c in slabs) == 1 << n and [f for f, _ in slabs] == [r << (n - int(np.log2(world))) for r in range(world)]
             spans.sort()
-            assert spans[0][0] == 0 and sum(c for _, c in spans) == 1 << (n - 12)
+            assert spans[0][0] == 0 and sum(c for _, c in spans) == 1 << (n - tile_bits)
             for (b0, c0), (b1, _) in zip(spans, spans[1:]):
                 assert b0 + c0 == b1
-    assert lib.b200vqe_debug_shard_layout(C.c_int(20), C.c_int(2), C.c_int(2), None, None, None, None) != 0
-    assert lib.b200vqe_debug_shard_layout(C.c_int(20), C.c_int(0), C.c_int(3), None, None, None, None) != 0
+    assert lib.b200vqe_debug_shard_layout(C.c_int(20), C.c_int(2), C.c_int(2), C.c_int(12), None, None, None, None) != 0
+    assert lib.b200vqe_debug_shard_layout(C.c_int(20), C.c_int(0), C.c_int(3), C.c_int(12), None, None, None, None) != 0

@@ -20,14 +20,14 @@ REC_DT = np.dtype([("kb", "<u4"), ("count", "<u4"), ("xv", "<u2"), ("key", "u1")
 STAGE_RECS, STAGE_TERMS = 128, 256          # capacities of one batch (kStageRecs / kStageTerms in csrc/tile_plan.hpp)
 
 
-def get_records(n, c, xm, zm, cf):
+def get_records(n, c, xm, zm, cf, tb=12):
     lib = xb.capi.lib()
     xm = np.ascontiguousarray(xm, np.uint64)
     zm = np.ascontiguousarray(zm, np.uint64)
     cr, ci = np.ascontiguousarray(cf.real), np.ascontiguousarray(cf.imag)
     nr = C.c_int64()
     vp = lambda a: a.ctypes.data_as(C.c_void_p)
-    args = (C.c_int(n), C.c_int(c), C.c_int64(len(xm)), vp(xm), vp(zm), vp(cr), vp(ci), C.byref(nr))
+    args = (C.c_int(n), C.c_int(c), C.c_int(tb), C.c_int64(len(xm)), vp(xm), vp(zm), vp(cr), vp(ci), C.byref(nr))
     assert lib.b200vqe_debug_tile_records(*args, None) == 0
     R = np.zeros(nr.value, REC_DT)
     assert REC_DT.itemsize == 32
@@ -35,14 +35,14 @@ def get_records(n, c, xm, zm, cf):
     return R
 
 
-def get_plan(n, c, xm, zm, cf):
+def get_plan(n, c, xm, zm, cf, tb=12):
     lib = xb.capi.lib()
     xm = np.ascontiguousarray(xm, np.uint64)
     zm = np.ascontiguousarray(zm, np.uint64)
     cr, ci = np.ascontiguousarray(cf.real), np.ascontiguousarray(cf.imag)
     nb, ng, nt = C.c_int64(), C.c_int64(), C.c_int64()
     vp = lambda a: a.ctypes.data_as(C.c_void_p)
-    args = (C.c_int(n), C.c_int(c), C.c_int64(len(xm)), vp(xm), vp(zm), vp(cr), vp(ci), C.byref(nb), C.byref(ng), C.byref(nt))
+    args = (C.c_int(n), C.c_int(c), C.c_int(tb), C.c_int64(len(xm)), vp(xm), vp(zm), vp(cr), vp(ci), C.byref(nb), C.byref(ng), C.byref(nt))
     assert lib.b200vqe_debug_tile_plan(*args, None, None, None) == 0
     B, G, T = np.zeros(nb.value, BATCH_DT), np.zeros(ng.value, GROUP_DT), np.zeros(nt.value, TERM_DT)
     assert BATCH_DT.itemsize == 128 and GROUP_DT.itemsize == 16 and TERM_DT.itemsize == 16
@@ -110,11 +110,13 @@ def replay(n, c, B, G, T, psi, tile_begin=0, tile_count=None):
     return total
 
 
-def replay_records(n, c, B, R, T, psi):
+def replay_records(n, c, B, R, T, psi, tb=12, tile_begin=0, tile_count=None):
     """What k_tile_expect computes from the TileRec records: per record, the key fixes WHICH (even / odd nY) and XR (the
     register part of the flip mask); XR != 0 visits the 8 registers with bit HS = top bit of XR clear, XR == 0 visits all."""
-    M = TILE_BITS - c
-    v = np.arange(1 << TILE_BITS, dtype=np.uint64)
+    M = tb - c
+    n_tiles = 1 << (n - tb)
+    tile_count = n_tiles if tile_count is None else tile_count
+    v = np.arange(1 << tb, dtype=np.uint64)
     mu = v >> np.uint64(c)
     lo = v & np.uint64((1 << c) - 1)
     total = 0.0
@@ -122,10 +124,10 @@ def replay_records(n, c, B, R, T, psi):
         recs = R[b["r_begin"]:b["r_end"]]
         assert len(recs) <= STAGE_RECS and b["t_end"] - b["t_begin"] <= STAGE_TERMS
         assert list(recs["key"]) == sorted(recs["key"]) and np.all(recs["pad0"] == 0)
-        combo = np.zeros(1 << TILE_BITS, np.uint64)
+        combo = np.zeros(1 << tb, np.uint64)
         for i in range(M):
             combo ^= np.where((mu >> np.uint64(i)) & np.uint64(1), np.uint64(b["basis"][i]), np.uint64(0)).astype(np.uint64)
-        for t in range(1 << (n - TILE_BITS)):
+        for t in range(tile_begin, tile_begin + tile_count):
             rep = 0
             for i in range(11):
                 rep |= (t & int(b["seg"][i])) << i
@@ -192,6 +194,11 @@ def test_plan_replay_matches_oracle(n, T, c, seed, weights):
     assert abs(e - eo.real) < 1e-11 * np.abs(cf).sum()
     er = replay_records(n, c, B, get_records(n, c, xm, zm, cf), Tt, psi)
     assert abs(er - eo.real) < 1e-11 * np.abs(cf).sum()
+    # 2048-amplitude tiles (3 register bits) of the double-buffered kernel
+    if c <= 8:
+        B2, G2, T2 = get_plan(n, c, xm, zm, cf, tb=11)
+        e2 = replay_records(n, c, B2, get_records(n, c, xm, zm, cf, tb=11), T2, psi, tb=11)
+        assert abs(e2 - eo.real) < 1e-11 * np.abs(cf).sum()
 
 
 def test_batch_capacity_splits_large_groups_and_batches():

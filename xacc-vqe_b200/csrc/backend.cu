@@ -110,9 +110,23 @@ static int make_slabs(b200vqe_ctx *h, const double2 *src, Slabs &s) {
     if (h->world == 1) { s.p[0] = src; return 0; }
     int rc = ensure_gather(h);
     if (rc) return rc;
-    NK(g_nccl.AllGather(src, h->gather, h->nloc * 2, ncclDouble, h->comm, h->stream));
+    // the gather runs on its own stream: it starts once everything queued so far (producers of src, earlier readers of
+    // the staging buffer) is done, and kernels that only read the local slab may be queued behind it on the main stream
+    // without waiting; wait_gather() orders the main stream after it before the first remote read
+    CK(cudaEventRecord(h->ev_src_ready, h->stream));
+    CK(cudaStreamWaitEvent(h->comm_stream, h->ev_src_ready, 0));
+    NK(g_nccl.AllGather(src, h->gather, h->nloc * 2, ncclDouble, h->comm, h->comm_stream));
+    CK(cudaEventRecord(h->ev_gathered, h->comm_stream));
+    h->gather_pending = true;
     for (int t = 0; t < h->world; ++t) s.p[t] = h->gather + (size_t)t * h->nloc;
     s.p[h->rank] = src;
+    return 0;
+}
+
+static int wait_gather(b200vqe_ctx *h) {
+    if (!h->gather_pending) return 0;
+    CK(cudaStreamWaitEvent(h->stream, h->ev_gathered, 0));
+    h->gather_pending = false;
     return 0;
 }
 
@@ -189,6 +203,9 @@ static int create_common(int n_qubits, int device, int rank, int world, const ch
     if ((e = cudaMalloc(&h->d_out, sizeof(double) * kOutDoubles)) != cudaSuccess) return fail(cudaGetErrorString(e), B200VQE_ENOMEM);
     if ((e = cudaMallocHost(&h->h_out, sizeof(double) * kOutDoubles)) != cudaSuccess) return fail(cudaGetErrorString(e), B200VQE_ENOMEM);
     if (world > 1) {
+        if ((e = cudaStreamCreateWithFlags(&h->comm_stream, cudaStreamNonBlocking)) != cudaSuccess) return fail(cudaGetErrorString(e), B200VQE_ECUDA);
+        cudaEventCreateWithFlags(&h->ev_src_ready, cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&h->ev_gathered, cudaEventDisableTiming);
         if (!g_nccl.load(g_err)) { delete h; return B200VQE_ECOMM; }
         ncclUniqueId u;
         memcpy(&u, id, 128);
@@ -211,6 +228,7 @@ int b200vqe_destroy(b200vqe_handle h) {
     if (!h) return 0;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
+    if (h->comm_stream) { cudaStreamSynchronize(h->comm_stream); cudaStreamDestroy(h->comm_stream); cudaEventDestroy(h->ev_src_ready); cudaEventDestroy(h->ev_gathered); }
     for (auto p : h->slots) if (p) cudaFree(p);
     if (h->gather) cudaFree(h->gather);
     if (h->xbuf) cudaFree(h->xbuf);
@@ -267,6 +285,12 @@ int b200vqe_set_option(b200vqe_handle h, const char *key, const char *value) {
         const int c = atoi(value);
         if (c < 2 || c > 8) FAIL(B200VQE_EINVAL, "tile-chunk-bits must be in [2, 8]");
         h->opt_tile_chunk_bits = c;
+        return 0;
+    }
+    if (k == "tile-bits") {
+        const int c = atoi(value);
+        if (c != kTileBitsSmall && c != kTileBits) FAIL(B200VQE_EINVAL, "tile-bits must be 11 or 12");
+        h->opt_tile_bits = c;
         return 0;
     }
     if (k == "tile-ctas-per-sm") {

@@ -37,7 +37,7 @@ struct DeviceHam {
     // per-term path (host copies, sorted by xmask): caller index, masks, r_k
     std::vector<int64_t> pt_idx; std::vector<uint64_t> pt_x, pt_z; std::vector<int> pt_ny;
     // tile engine (kernels_tile.cuh): batches of xmask groups evaluated per HBM read of the state
-    int tile_C = 0, tile_M = 0, n_tile_batches = 0, n_tile_groups = 0;
+    int tile_C = 0, tile_M = 0, tile_TB = kTileBits, n_tile_batches = 0, n_tile_groups = 0;
     TileBatch *tl_batches = nullptr; TileRec *tl_recs = nullptr; TileTerm *tl_terms = nullptr;
     // tile engine for H psi: one plan per x_rank class (which peer slab the partners live in), concatenated
     struct ApplyClass { int x_rank; int b_begin, b_end; };
@@ -68,6 +68,8 @@ struct b200vqe_ctx {
     int n = 0, nl = 0, device = 0, rank = 0, world = 1, n_sm = 148, smem_optin = 0;
     uint64_t nloc = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t comm_stream = nullptr;             // sharded only: the all-gather runs here, overlapped with local groups
+    cudaEvent_t ev_src_ready = nullptr, ev_gathered = nullptr; bool gather_pending = false;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_t0 = nullptr, ev_t1 = nullptr;
     std::vector<double2 *> slots;
     double2 *gather = nullptr;          // [world][nloc] staging of the peers' shards
@@ -86,5 +88,6 @@ struct b200vqe_ctx {
     int opt_expect_engine = 0;          // 0 auto, 1 tile engine, 2 streaming kernel
     int opt_apply_engine = 0;           // same, for H psi
     int opt_tile_ctas = 2;              // resident CTAs per SM of the tile engine (2 or 3)
+    int opt_tile_bits = 12;             // tile of the <psi|H|psi> engine: 12 = 4096 amplitudes single-buffered, 11 = 2048 double-buffered
     int opt_tile_chunk_bits = 3;        // C: contiguous amplitudes per chunk = 2^C (128 B at C = 3)
 };

@@ -108,40 +108,47 @@ __device__ __forceinline__ void tile_class(const double2 (&a)[16], const double2
 // A record is the even-nY (WHICH = 0, uses Re w) or odd-nY (WHICH = 1, uses Im w) terms of one xmask group,
 // w = conj(psi[j^x]) psi[j].  The record's key fixes WHICH and XR = xv >> 8 at COMPILE time (records of a batch are
 // sorted by key, one specialised loop per key), so the partner of register r is row r ^ XR of thread v0 ^ xt:
-// eight LDS.128 at immediate offsets from one per-record address.
-//   XR != 0: HS = top bit of XR; a thread visits its 8 registers with bit HS clear (each pair once, weight 2 in u).
-//   XR == 0: the partner sits in the same row; all 16 registers are visited (two halves of 8), weight 1.
+// LDS.128 at immediate offsets from one per-record address.  RB = register bits of the tile (4: 16 amplitudes per
+// thread, 3: 8 amplitudes per thread); NP = 2^(RB-1) pairs per thread per record.
+//   XR != 0: HS = top bit of XR; a thread visits its NP registers with bit HS clear (each pair once, weight 2 in u).
+//   XR == 0: the partner sits in the same row; all registers are visited (two halves of NP), weight 1.
 template <int XR> struct XrInfo { static constexpr int HS = XR >= 8 ? 3 : (XR >= 4 ? 2 : (XR >= 2 ? 1 : 0)); };
 
-// one term on the 8 products w[]: sign = thread constant (one POPC) x Walsh function of the visited registers
-template <int HS, int BV>
-__device__ __forceinline__ void tile_term(const double (&w)[8], unsigned long long packed, double u, unsigned v0, unsigned rep,
-                                          double &acc) {
+__device__ __forceinline__ double signed_sum(const double (&w)[8], double s0, double s1, double s2) { return signed_sum8(w, s0, s1, s2); }
+__device__ __forceinline__ double signed_sum(const double (&w)[4], double s0, double s1, double) {
+    return fma(s1, fma(s0, w[3], w[2]), fma(s0, w[1], w[0]));
+}
+
+// one term on the NP products w[]: sign = thread constant (one POPC) x Walsh function of the visited registers
+template <int RB, int HS, int BV>
+__device__ __forceinline__ void tile_term(const double (&w)[1 << (RB - 1)], unsigned long long packed, double u, unsigned v0,
+                                          unsigned rep, double &acc) {
     const unsigned zl = (unsigned)packed;                     // z on the high index bits
-    const unsigned hw = (unsigned)(packed >> 32);             // bits 0..7: thread bits of zv, 8..11: register bits
+    const unsigned hw = (unsigned)(packed >> 32);             // bits 0..7: thread bits of zv, 8..8+RB-1: register bits
     // coset part and thread part share one POPC: parity(a) ^ parity(b) = parity(a ^ b)
     unsigned par = (unsigned)__popc((rep & zl) ^ (v0 & hw & 0xffu));
     if (BV) par += hw >> (8 + HS);
     // free register bits: i-bit k <-> r-bit (k < HS ? k : k + 1)
     const double s0 = pm_one_hi(hw, 8 + (0 < HS ? 0 : 1));
     const double s1 = pm_one_hi(hw, 8 + (1 < HS ? 1 : 2));
-    const double s2 = pm_one_hi(hw, 8 + (2 < HS ? 2 : 3));
+    const double s2 = RB == 4 ? pm_one_hi(hw, 8 + (2 < HS ? 2 : 3)) : 1.0;
     const double us = __hiloint2double(__double2hiint(u) ^ (int)(par << 31), __double2loint(u));
-    acc = fma(us, signed_sum8(w, s0, s1, s2), acc);
+    acc = fma(us, signed_sum(w, s0, s1, s2), acc);
 }
 
-template <int WHICH, int XR, int BV>
-__device__ __forceinline__ void tile_rec_half(const double2 (&a)[16], const double2 *__restrict__ P, unsigned v0, unsigned rep,
+template <int RB, int WHICH, int XR, int BV>
+__device__ __forceinline__ void tile_rec_half(const double2 (&a)[1 << RB], const double2 *__restrict__ P, unsigned v0, unsigned rep,
                                               const int4 ra, const int4 rb, const double2 *__restrict__ s_terms, double &acc) {
-    constexpr int HS = XR ? XrInfo<XR>::HS : 3;
-    double w[8];
+    constexpr int HS = XR ? XrInfo<XR>::HS : RB - 1;
+    constexpr int NP = 1 << (RB - 1);
+    double w[NP];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
+    for (int i = 0; i < NP; ++i) {
         const int r = ((i >> HS) << (HS + 1)) | (BV << HS) | (i & ((1 << HS) - 1));
         const double2 b = P[(r ^ XR) << 8];
         w[i] = WHICH == 0 ? fma(b.x, a[r].x, b.y * a[r].y) : fma(b.x, a[r].y, -(b.y * a[r].x));
     }
-    tile_term<HS, BV>(w, ((unsigned long long)(unsigned)rb.y << 32) | (unsigned)rb.x, __hiloint2double(rb.w, rb.z), v0, rep, acc);
+    tile_term<RB, HS, BV>(w, ((unsigned long long)(unsigned)rb.y << 32) | (unsigned)rb.x, __hiloint2double(rb.w, rb.z), v0, rep, acc);
     const int count = ra.y;
     if (count > 1) {
         const double2 *tp = s_terms + ra.x;
@@ -150,35 +157,31 @@ __device__ __forceinline__ void tile_rec_half(const double2 (&a)[16], const doub
         for (int e = 1; e < count; ++e) {
             const double2 c = t;
             if (e + 1 < count) t = tp[e + 1];
-            tile_term<HS, BV>(w, (unsigned long long)__double_as_longlong(c.x), c.y, v0, rep, acc);
+            tile_term<RB, HS, BV>(w, (unsigned long long)__double_as_longlong(c.x), c.y, v0, rep, acc);
         }
     }
 }
 
-template <int K>
-__device__ __forceinline__ void tile_rec(const double2 (&a)[16], const double2 *__restrict__ tile, unsigned v0, unsigned rep,
-                                         const int4 ra, const int4 rb, const double2 *__restrict__ s_terms, double &acc) {
-    constexpr int WHICH = K >> 4;
-    constexpr int XR = ((K & 15) + 1) & 15;
-    const double2 *P = tile + ((v0 ^ (unsigned)ra.z) & 0xffu);         // row 0 of the partner thread
-    tile_rec_half<WHICH, XR, 0>(a, P, v0, rep, ra, rb, s_terms, acc);
-    if (XR == 0) tile_rec_half<WHICH, XR, 1>(a, P, v0, rep, ra, rb, s_terms, acc);
-}
-
 // all records of the batch, key by key: s_recs holds (n_r + 1) records as int4 pairs, the last one a sentinel (key 255)
-template <int K>
-__device__ __forceinline__ void tile_runs(const double2 (&a)[16], const double2 *__restrict__ tile, unsigned v0, unsigned rep,
+template <int RB, int K>
+__device__ __forceinline__ void tile_runs(const double2 (&a)[1 << RB], const double2 *__restrict__ tile, unsigned v0, unsigned rep,
                                           const int4 *__restrict__ s_recs, const double2 *__restrict__ s_terms, int &gi, int4 &ra,
                                           int4 &rb, double &acc) {
     if constexpr (K < kTileRecKeys) {
-        while (((unsigned)ra.z >> 16) == (unsigned)K) {
-            const int4 ca = ra, cb = rb;
-            ++gi;
-            ra = s_recs[2 * gi];                                       // next record (or the sentinel)
-            rb = s_recs[2 * gi + 1];
-            tile_rec<K>(a, tile, v0, rep, ca, cb, s_terms, acc);
+        constexpr int WHICH = K >> 4;
+        constexpr int XR = ((K & 15) + 1) & 15;
+        if constexpr (XR < (1 << RB)) {
+            while (((unsigned)ra.z >> 16) == (unsigned)K) {
+                const int4 ca = ra, cb = rb;
+                ++gi;
+                ra = s_recs[2 * gi];                                   // next record (or the sentinel)
+                rb = s_recs[2 * gi + 1];
+                const double2 *P = tile + ((v0 ^ (unsigned)ca.z) & 0xffu);     // row 0 of the partner thread
+                tile_rec_half<RB, WHICH, XR, 0>(a, P, v0, rep, ca, cb, s_terms, acc);
+                if (XR == 0) tile_rec_half<RB, WHICH, XR, 1>(a, P, v0, rep, ca, cb, s_terms, acc);
+            }
         }
-        tile_runs<K + 1>(a, tile, v0, rep, s_recs, s_terms, gi, ra, rb, acc);
+        tile_runs<RB, K + 1>(a, tile, v0, rep, s_recs, s_terms, gi, ra, rb, acc);
     }
 }
 
@@ -269,8 +272,113 @@ k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_byte
         }
         int gi = 0;
         int4 ra = s_recs[0], rb = s_recs[1];
-        tile_runs<0>(a, tile, v0, rep, s_recs, s_terms, gi, ra, rb, acc);
+        tile_runs<4, 0>(a, tile, v0, rep, s_recs, s_terms, gi, ra, rb, acc);
     }
+    double v[1] = {acc};
+    grid_reduce<1>(v, partials, counter, out, 1.0);
+}
+
+// ---------------------------------------------------------------------------------------------
+// <psi|H|psi>, double-buffered: 2048-amplitude tiles (RB = 3, 8 amplitudes per thread, 32 KB), two tile buffers per CTA,
+// three CTAs per SM.  While the records of the current tile are walked, the CTA's next tile streams from HBM into the
+// other buffer with cp.async (16 B per thread per row, no registers, no LSU store), so the load latency that the
+// single-buffer kernel exposes at every tile is hidden and 24 warps per SM keep the shared-memory pipe busy.
+// A thread reads its own 8 amplitudes back from the tile (8 LDS.128: what the register path spends on stores).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+template <int RB>
+__global__ void __launch_bounds__(kBlock, 3)
+k_tile_expect_db(const double2 *__restrict__ psi, int C, int M, unsigned chunk_bytes, const TileBatch *__restrict__ batches, int n_batches,
+                 unsigned long long tile_begin, unsigned long long tile_count, const TileRec *__restrict__ recs,
+                 const TileTerm *__restrict__ terms, double *partials, unsigned *counter, double *out) {
+    constexpr int REGS = 1 << RB;
+    constexpr unsigned TILE = 256u << RB;                 // amplitudes per tile buffer
+    extern __shared__ __align__(16) unsigned char tile_raw[];
+    double2 *buf = reinterpret_cast<double2 *>(tile_raw);  // [2][TILE]
+    __shared__ TileBatch sb;
+    __shared__ __align__(16) int4 s_recs[2 * (kStageRecs + 1)];
+    __shared__ __align__(16) double2 s_terms[kStageTerms];
+    const unsigned v0 = threadIdx.x;
+    const unsigned lo = v0 & ((1u << C) - 1u);
+    double acc = 0.0;
+    int cur_b = -1;
+    unsigned Tc = 0, rbv[RB];
+    const char *psi_lo = reinterpret_cast<const char *>(psi + lo);   // chunk hi of this thread's column: psi_lo + hi * chunk_bytes
+    const unsigned long long total = (unsigned long long)n_batches * tile_count;
+    unsigned p = 0;                      // buffer holding the current tile
+    bool in_flight = false;              // the current tile was requested during the previous iteration
+    unsigned rep = 0;
+
+    auto request = [&](unsigned rep_t, unsigned which) {      // this thread's REGS rows of the tile with representative rep_t
+        const unsigned base = rep_t ^ Tc;
+        double2 *dst = buf + which * TILE + v0;
+#pragma unroll
+        for (int r = 0; r < REGS; ++r) {
+            unsigned hi = base;
+#pragma unroll
+            for (int k = 0; k < RB; ++k) if (r & (1 << k)) hi ^= rbv[k];
+            cp_async16(dst + ((unsigned)r << 8), psi_lo + (unsigned long long)hi * chunk_bytes);
+        }
+        cp_async_commit();
+    };
+
+    for (unsigned long long w = blockIdx.x; w < total; w += gridDim.x) {
+        const int b = (int)(w / tile_count);
+        if (b != cur_b) {                       // uniform over the CTA; no request is in flight across a batch switch
+            __syncthreads();
+            if (threadIdx.x < 32)
+                reinterpret_cast<uint32_t *>(&sb)[threadIdx.x] = reinterpret_cast<const uint32_t *>(&batches[b])[threadIdx.x];
+            __syncthreads();
+            cur_b = b;
+            Tc = 0;
+            for (int i = 0; i < 8 - C; ++i) if ((v0 >> (C + i)) & 1u) Tc ^= sb.basis[i];
+#pragma unroll
+            for (int k = 0; k < RB; ++k) rbv[k] = sb.basis[M - RB + k];
+            const int n_r = sb.r_end - sb.r_begin;
+            const int n_t = sb.t_end - sb.t_begin;
+            const int4 *rsrc = reinterpret_cast<const int4 *>(recs + sb.r_begin);
+            for (int i = threadIdx.x; i < 2 * n_r; i += kBlock) {
+                int4 q = rsrc[i];
+                if (!(i & 1)) q.x -= sb.t_begin;
+                s_recs[i] = q;
+            }
+            if (threadIdx.x == 0) s_recs[2 * n_r] = make_int4(0, 0, 0xff << 16, 0);
+            const double2 *tsrc = reinterpret_cast<const double2 *>(terms) + sb.t_begin;
+            for (int i = threadIdx.x; i < n_t; i += kBlock) s_terms[i] = tsrc[i];
+            in_flight = false;
+        }
+        if (!in_flight) {
+            rep = tile_rep(sb, (unsigned)(tile_begin + (w - (unsigned long long)b * tile_count)));
+            request(rep, p);
+        }
+        cp_async_wait_all();
+        __syncthreads();                        // the current tile is complete; everyone is done with the other buffer
+        unsigned rep_next = 0;
+        {
+            const unsigned long long wn = w + gridDim.x;
+            in_flight = wn < total && wn / tile_count == (unsigned long long)b;
+            if (in_flight) {
+                rep_next = tile_rep(sb, (unsigned)(tile_begin + (wn - (unsigned long long)b * tile_count)));
+                request(rep_next, p ^ 1u);
+            }
+        }
+        const double2 *tile = buf + p * TILE;
+        double2 a[REGS];
+#pragma unroll
+        for (int r = 0; r < REGS; ++r) a[r] = tile[((unsigned)r << 8) | v0];
+        int gi = 0;
+        int4 ra = s_recs[0], rb = s_recs[1];
+        tile_runs<RB, 0>(a, tile, v0, rep, s_recs, s_terms, gi, ra, rb, acc);
+        rep = rep_next;
+        p ^= 1u;
+    }
+    cp_async_wait_all();
     double v[1] = {acc};
     grid_reduce<1>(v, partials, counter, out, 1.0);
 }

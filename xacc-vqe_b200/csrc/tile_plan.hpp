@@ -22,8 +22,10 @@
 
 namespace b200vqe {
 
-constexpr int kTileBits = 12;        // tile = 4096 amplitudes = 64 KB of double2
+constexpr int kTileBits = 12;        // largest tile = 4096 amplitudes = 64 KB of double2 (H psi, sweep, single-buffer <psi|H|psi>)
 constexpr int kTileRegBits = 4;      // 16 amplitudes per thread (virtual bits 8..11)
+constexpr int kTileBitsSmall = 11;   // 2048-amplitude tiles, 8 per thread: the double-buffered <psi|H|psi> kernel
+constexpr int kTileThreadBits = 8;   // 256 threads per CTA: virtual bits 0..7 of a tile index are the thread
 constexpr int kTileMaxDim = 10;      // M = kTileBits - C, C >= 2
 
 constexpr int kTileClasses = 5;      // groups of a batch are ordered by hsel = 0, 1, 2, 3, -1
@@ -77,7 +79,7 @@ constexpr int kStageGroupsCap = kStageRecs / 2;
 struct TilePlanTermIn { uint64_t x, z; double u; int odd; int64_t idx; };
 
 struct TilePlan {
-    int n = 0, C = 0, M = 0;
+    int n = 0, C = 0, M = 0, TB = kTileBits;
     std::vector<TileBatch> batches;
     std::vector<TileGroup> groups;
     std::vector<TileTerm> terms;
@@ -87,8 +89,8 @@ struct TilePlan {
 
 // Which tiles (cosets) of every batch a rank of a sharded register evaluates in <psi|H|psi>: a contiguous 1/world share;
 // registers with fewer tiles than ranks are evaluated by rank 0 alone.  The union over ranks is every tile exactly once.
-inline void shard_tile_range(int n, int rank, int world, uint64_t &begin, uint64_t &count) {
-    const uint64_t all = 1ull << (n - kTileBits);
+inline void shard_tile_range(int n, int rank, int world, uint64_t &begin, uint64_t &count, int tile_bits = kTileBits) {
+    const uint64_t all = 1ull << (n - tile_bits);
     const uint64_t per = all / (uint64_t)world;
     if (per) { begin = per * (uint64_t)rank; count = per; }
     else { begin = 0; count = rank == 0 ? all : 0; }
@@ -137,10 +139,11 @@ inline uint16_t sign_word16(unsigned zr) {   // bit r = parity(r & zr), r = 0..1
 // max_groups / max_terms (0 = unlimited): capacity of one batch; an xmask group with more terms than max_terms is cut
 // into several groups of the same x.
 inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> &in, bool pair_weights = true, bool natural = false,
-                                size_t max_groups = 0, size_t max_terms = 0) {
+                                size_t max_groups = 0, size_t max_terms = 0, int tile_bits = kTileBits) {
     using namespace tileplan;
+    const int TB = tile_bits, RB = tile_bits - kTileThreadBits;      // tile bits, register bits (4 or 3)
     TilePlan P;
-    P.n = n; P.C = C; P.M = kTileBits - C;
+    P.n = n; P.C = C; P.M = TB - C; P.TB = TB;
     const int M = P.M;
     const int nh = n - C;                         // bits of the high index
     const uint64_t lomask = (1ull << C) - 1;
@@ -208,7 +211,7 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
             }
             members.resize(keep);
         }
-        // ---- order the basis: the kTileRegBits coordinates that cover most work go on the register bits ----
+        // ---- order the basis: the RB coordinates that cover most work go on the register bits ----
         const int dim = (int)rr.b.size();
         std::vector<uint64_t> mu(members.size());
         std::vector<double> cost(members.size());
@@ -219,7 +222,7 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
         std::vector<int> perm;                     // perm[new position] = old index
         std::vector<char> used(dim, 0), covered(members.size(), 0);
         std::vector<int> top;
-        for (int pick = 0; pick < kTileRegBits && pick < dim; ++pick) {
+        for (int pick = 0; pick < RB && pick < dim; ++pick) {
             int best = -1;
             double bestw = -1.0;
             for (int i = 0; i < dim; ++i) {
@@ -237,7 +240,7 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
             for (int i = 0; i < dim; ++i) perm.push_back(dim - 1 - i);     // virtual bit C+i <-> high bit i
         } else {
             for (int i = 0; i < dim; ++i) if (!used[i]) perm.push_back(i);
-            for (int t : top) perm.push_back(t);       // register bits are the top kTileRegBits coordinates
+            for (int t : top) perm.push_back(t);       // register bits are the top RB coordinates
         }
 
         TileBatch B{};
@@ -263,7 +266,7 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
         };
         // order the members by pair-selector class (hsel 0, 1, 2, 3, then -1): one code path per class on the device
         auto class_of = [&](size_t k) {
-            const unsigned xr = (unsigned)(((permute_mu(mu[k]) << C) >> (kTileBits - kTileRegBits)) & ((1u << kTileRegBits) - 1));
+            const unsigned xr = (unsigned)(((permute_mu(mu[k]) << C) >> (TB - RB)) & ((1u << RB) - 1));
             return xr ? 31 - __builtin_clz(xr) : kTileClasses - 1;
         };
         std::vector<size_t> ord(members.size());
@@ -277,7 +280,7 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
             const uint64_t m = permute_mu(mu[k]);
             TileGroup tg{};
             tg.xv = (uint16_t)((m << C) | (g.x & lomask));
-            const unsigned xr = tg.xv >> (kTileBits - kTileRegBits);
+            const unsigned xr = tg.xv >> (TB - RB);
             tg.hsel = xr ? (int16_t)(31 - __builtin_clz(xr)) : (int16_t)-1;
             const double weight = tg.hsel >= 0 ? 2.0 : 1.0;
             tg.kb = (uint32_t)P.terms.size();
@@ -289,8 +292,8 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
                 const unsigned zv = (unsigned)((Zv << C) | (ti.z & lomask));
                 TileTerm tt;
                 tt.packed = (zhi & 0xffffffffull) | ((uint64_t)(zv & 0xffu) << 32) |
-                            ((uint64_t)((zv >> (kTileBits - kTileRegBits)) & 0xfu) << 40) |
-                            ((uint64_t)sign_word16((zv >> (kTileBits - kTileRegBits)) & 0xfu) << 48);
+                            ((uint64_t)((zv >> (TB - RB)) & 0xfu) << 40) |
+                            ((uint64_t)sign_word16((zv >> (TB - RB)) & 0xfu) << 48);
                 tt.u = (pair_weights ? weight : 1.0) * ti.u;
                 P.terms.push_back(tt);
                 P.term_src.push_back(ti.idx);
@@ -314,7 +317,7 @@ inline void build_tile_records(TilePlan &P) {
         std::vector<TileRec> rs;
         for (int g = B.g_begin; g < B.g_end; ++g) {
             const TileGroup &tg = P.groups[g];
-            const unsigned xr = tg.xv >> (kTileBits - kTileRegBits);
+            const unsigned xr = tg.xv >> kTileThreadBits;
             for (int which = 0; which < 2; ++which) {
                 const uint32_t cnt = which ? tg.n_odd : tg.n_even;
                 if (!cnt) continue;
