@@ -220,6 +220,8 @@ def run_gpu(args):
         if apply_op:
             be.apply_h(0, 1, want_alpha=False)      # dst = H psi (one Lanczos matrix-vector product)
             return 0j
+        if args.op == "terms":
+            return be.expectation(per_term=True)[0]     # energy + per-term <P_k> (the reference's per-kernel exp-val-z)
         return be.expectation()
 
     def barrier():
@@ -298,7 +300,7 @@ def run_gpu(args):
     peak, peak_src = measured_peak_gbs()
     # algorithmic bytes of one <psi|H|psi> on one GPU: 16 B x local amplitudes x groups
     alg_bytes = 16.0 * be.n_local * (G + 1 if apply_op else G)
-    k_ms = float(np.mean(kernel_ms))
+    k_ms = ms_per_step if args.op == "terms" else float(np.mean(kernel_ms))     # terms: energy launch + per-term launch
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
     traffic = traffic_tile = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
@@ -329,7 +331,7 @@ def run_gpu(args):
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": {"workload": f"synthetic {n}-qubit random Pauli sum, {Tn} terms, fp64 " + ("H.psi" if apply_op else "<psi|H|psi>"),
+            "config": {"workload": f"synthetic {n}-qubit random Pauli sum, {Tn} terms, fp64 " + ("H.psi" if apply_op else ("<psi|H|psi> + per-term <P_k>" if args.op == "terms" else "<psi|H|psi>")),
                        "n_qubits": n, "n_terms": int(Tn), "n_xmask_groups": int(G), "amplitudes_per_gpu": int(be.n_local),
                        "parallelism": f"state sharded over {world} GPU(s) by high index bits",
                        "l2": "inputs larger than L2 (4.3 GB state per GPU vs 126 MB)"},
@@ -376,7 +378,7 @@ def main():
     ap.add_argument("--terms", type=int, default=N_TERMS)
     ap.add_argument("--cpu-terms", type=int, default=256, help="terms in the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--op", default="expect", choices=["expect", "apply"], help="expect: <psi|H|psi> (headline); apply: dst = H psi")
+    ap.add_argument("--op", default="expect", choices=["expect", "apply", "terms"], help="expect: <psi|H|psi> (headline); apply: dst = H psi; terms: <psi|H|psi> plus every <P_k>")
     ap.add_argument("--engine", default="auto", choices=["auto", "tile", "stream"], help="<psi|H|psi> kernel family")
     ap.add_argument("--tile-ctas", type=int, default=2, choices=[2, 3], help="tile engine: resident CTAs per SM")
     ap.add_argument("--tile-bits", type=int, default=12, choices=[11, 12], help="tile engine: 12 = 4096-amplitude tiles, 11 = 2048 double-buffered")

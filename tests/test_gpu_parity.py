@@ -376,3 +376,38 @@ def test_number_symmetry_sector_lanczos(xb, golden, tr):
         A = po.dense_matrix_reference(oop, n)
         assert rel(e_full, np.linalg.eigvalsh(A)[0]) < REL
         be.close()
+
+
+@pytest.mark.parametrize("n,T,seed,structured", [(12, 40, 91, False), (15, 150, 92, False), (14, 500, 93, True), (18, 40, 94, False)])
+def test_per_term_expectations_on_the_tile_engine(xb, n, T, seed, structured):
+    """per_term (what getExpectationValueZ returns per kernel, ComputeEnergyVQETask.cpp:137-166; RDMGenerator.cpp:121) from
+    the tile engine's per-term mode against the 16-terms-per-sweep kernel and the oracle; identity term reads 1."""
+    if structured:
+        rng = np.random.default_rng(seed)
+        xs = rng.integers(0, 1 << 5, size=T, dtype=np.uint64) << np.uint64(2)
+        zs = rng.integers(0, 1 << n, size=T, dtype=np.uint64)
+        keys = sorted({(int(x), int(z)) for x, z in zip(xs, zs) if x or z})
+        xm = np.array([k[0] for k in keys] + [0], np.uint64)          # + the identity term
+        zm = np.array([k[1] for k in keys] + [0], np.uint64)
+        ny = np.array([bin(int(x) & int(z)).count("1") for x, z in zip(xm, zm)])
+        cf = rng.normal(size=len(xm)) * (1j ** (ny % 4))
+    else:
+        xm, zm, cf = random_hamiltonian(n, T, seed)
+    psi = random_state(n, seed + 100)
+    eo, pero = co.expect(n, xm, zm, cf, psi)
+    got = {}
+    for engine in ("tile", "stream"):
+        be = xb.Backend(n)
+        be.set_option("expect-engine", engine)
+        be.set_hamiltonian(xm, zm, cf)
+        be.upload(psi)
+        e, per = be.expectation(per_term=True)
+        assert abs(e - eo) < REL * np.abs(cf).sum()
+        ident = (xm | zm) == 0
+        assert np.all(per[ident] == 1.0)
+        assert np.abs(per[~ident] - pero.real[~ident]).max() < 1e-11, engine
+        _, per2 = be.expectation(per_term=True)
+        assert np.array_equal(per, per2)            # fixed summation order
+        got[engine] = per
+        be.close()
+    assert np.abs(got["tile"] - got["stream"]).max() < 1e-11

@@ -234,6 +234,8 @@ int b200vqe_destroy(b200vqe_handle h) {
     if (h->xbuf) cudaFree(h->xbuf);
     h->ham.free_device();
     cudaFree(h->partials); cudaFree(h->counter); cudaFree(h->d_out); cudaFreeHost(h->h_out);
+    if (h->d_term_partials) cudaFree(h->d_term_partials);
+    if (h->d_term_out) cudaFree(h->d_term_out);
     if (h->d_alpha) cudaFree(h->d_alpha);
     if (h->d_norm) cudaFree(h->d_norm);
     if (h->d_ritz) cudaFree(h->d_ritz);

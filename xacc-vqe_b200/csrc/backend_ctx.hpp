@@ -39,6 +39,9 @@ struct DeviceHam {
     // tile engine (kernels_tile.cuh): batches of xmask groups evaluated per HBM read of the state
     int tile_C = 0, tile_M = 0, tile_TB = kTileBits, n_tile_batches = 0, n_tile_groups = 0;
     TileBatch *tl_batches = nullptr; TileRec *tl_recs = nullptr; TileTerm *tl_terms = nullptr;
+    std::vector<int64_t> tl_term_idx;   // plan term -> caller index (per-term output of the tile engine)
+    std::vector<double> tl_term_u;      // unweighted coefficient of the plan term: coef (even nY) | i*coef (odd nY)
+    std::vector<double> tl_term_r;      // <P_k> = r_k * (signed pair sum): Re i^nY (even nY) | -Im i^nY (odd nY)
     // tile engine for H psi: one plan per x_rank class (which peer slab the partners live in), concatenated
     struct ApplyClass { int x_rank; int b_begin, b_end; };
     std::vector<ApplyClass> ta_classes;
@@ -78,6 +81,7 @@ struct b200vqe_ctx {
     double *partials = nullptr; unsigned *counter = nullptr;
     double *d_out = nullptr, *h_out = nullptr;
     double *d_alpha = nullptr, *d_norm = nullptr, *d_ritz = nullptr; int lanczos_cap = 0;
+    double *d_term_partials = nullptr, *d_term_out = nullptr; size_t term_partials_cap = 0, term_out_cap = 0;
     ncclComm_t comm = nullptr;
     std::string err;
     int64_t launches = 0;

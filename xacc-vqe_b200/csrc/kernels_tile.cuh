@@ -120,9 +120,11 @@ __device__ __forceinline__ double signed_sum(const double (&w)[4], double s0, do
 }
 
 // one term on the NP products w[]: sign = thread constant (one POPC) x Walsh function of the visited registers
-template <int RB, int HS, int BV>
+// PT (per-term output): the term's signed pair sum, without its coefficient, is reduced over the warp and added to the
+// warp's own accumulator of that term in shared memory (*slot; lane 0 only) -- what getExpectationValueZ() returns per kernel.
+template <int RB, int HS, int BV, bool PT = false>
 __device__ __forceinline__ void tile_term(const double (&w)[1 << (RB - 1)], unsigned long long packed, double u, unsigned v0,
-                                          unsigned rep, double &acc) {
+                                          unsigned rep, double &acc, double *slot = nullptr, double weight = 1.0) {
     const unsigned zl = (unsigned)packed;                     // z on the high index bits
     const unsigned hw = (unsigned)(packed >> 32);             // bits 0..7: thread bits of zv, 8..8+RB-1: register bits
     // coset part and thread part share one POPC: parity(a) ^ parity(b) = parity(a ^ b)
@@ -132,13 +134,22 @@ __device__ __forceinline__ void tile_term(const double (&w)[1 << (RB - 1)], unsi
     const double s0 = pm_one_hi(hw, 8 + (0 < HS ? 0 : 1));
     const double s1 = pm_one_hi(hw, 8 + (1 < HS ? 1 : 2));
     const double s2 = RB == 4 ? pm_one_hi(hw, 8 + (2 < HS ? 2 : 3)) : 1.0;
-    const double us = __hiloint2double(__double2hiint(u) ^ (int)(par << 31), __double2loint(u));
-    acc = fma(us, signed_sum(w, s0, s1, s2), acc);
+    if (!PT) {
+        const double us = __hiloint2double(__double2hiint(u) ^ (int)(par << 31), __double2loint(u));
+        acc = fma(us, signed_sum(w, s0, s1, s2), acc);
+    } else {
+        const double ws = __hiloint2double(__double2hiint(weight) ^ (int)(par << 31), 0);      // +-1.0 or +-2.0
+        double v = ws * signed_sum(w, s0, s1, s2);
+#pragma unroll
+        for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((v0 & 31u) == 0) *slot += v;
+    }
 }
 
-template <int RB, int WHICH, int XR, int BV>
+template <int RB, int WHICH, int XR, int BV, bool PT = false>
 __device__ __forceinline__ void tile_rec_half(const double2 (&a)[1 << RB], const double2 *__restrict__ P, unsigned v0, unsigned rep,
-                                              const int4 ra, const int4 rb, const double2 *__restrict__ s_terms, double &acc) {
+                                              const int4 ra, const int4 rb, const double2 *__restrict__ s_terms, double &acc,
+                                              double *part = nullptr) {
     constexpr int HS = XR ? XrInfo<XR>::HS : RB - 1;
     constexpr int NP = 1 << (RB - 1);
     double w[NP];
@@ -148,7 +159,9 @@ __device__ __forceinline__ void tile_rec_half(const double2 (&a)[1 << RB], const
         const double2 b = P[(r ^ XR) << 8];
         w[i] = WHICH == 0 ? fma(b.x, a[r].x, b.y * a[r].y) : fma(b.x, a[r].y, -(b.y * a[r].x));
     }
-    tile_term<RB, HS, BV>(w, ((unsigned long long)(unsigned)rb.y << 32) | (unsigned)rb.x, __hiloint2double(rb.w, rb.z), v0, rep, acc);
+    constexpr double WEIGHT = XR ? 2.0 : 1.0;      // each pair once | every amplitude
+    tile_term<RB, HS, BV, PT>(w, ((unsigned long long)(unsigned)rb.y << 32) | (unsigned)rb.x, __hiloint2double(rb.w, rb.z), v0, rep, acc,
+                              PT ? part + ra.x : nullptr, WEIGHT);
     const int count = ra.y;
     if (count > 1) {
         const double2 *tp = s_terms + ra.x;
@@ -157,16 +170,16 @@ __device__ __forceinline__ void tile_rec_half(const double2 (&a)[1 << RB], const
         for (int e = 1; e < count; ++e) {
             const double2 c = t;
             if (e + 1 < count) t = tp[e + 1];
-            tile_term<RB, HS, BV>(w, (unsigned long long)__double_as_longlong(c.x), c.y, v0, rep, acc);
+            tile_term<RB, HS, BV, PT>(w, (unsigned long long)__double_as_longlong(c.x), c.y, v0, rep, acc, PT ? part + ra.x + e : nullptr, WEIGHT);
         }
     }
 }
 
 // all records of the batch, key by key: s_recs holds (n_r + 1) records as int4 pairs, the last one a sentinel (key 255)
-template <int RB, int K>
+template <int RB, int K, bool PT = false>
 __device__ __forceinline__ void tile_runs(const double2 (&a)[1 << RB], const double2 *__restrict__ tile, unsigned v0, unsigned rep,
                                           const int4 *__restrict__ s_recs, const double2 *__restrict__ s_terms, int &gi, int4 &ra,
-                                          int4 &rb, double &acc) {
+                                          int4 &rb, double &acc, double *part = nullptr) {
     if constexpr (K < kTileRecKeys) {
         constexpr int WHICH = K >> 4;
         constexpr int XR = ((K & 15) + 1) & 15;
@@ -177,11 +190,11 @@ __device__ __forceinline__ void tile_runs(const double2 (&a)[1 << RB], const dou
                 ra = s_recs[2 * gi];                                   // next record (or the sentinel)
                 rb = s_recs[2 * gi + 1];
                 const double2 *P = tile + ((v0 ^ (unsigned)ca.z) & 0xffu);     // row 0 of the partner thread
-                tile_rec_half<RB, WHICH, XR, 0>(a, P, v0, rep, ca, cb, s_terms, acc);
-                if (XR == 0) tile_rec_half<RB, WHICH, XR, 1>(a, P, v0, rep, ca, cb, s_terms, acc);
+                tile_rec_half<RB, WHICH, XR, 0, PT>(a, P, v0, rep, ca, cb, s_terms, acc, part);
+                if (XR == 0) tile_rec_half<RB, WHICH, XR, 1, PT>(a, P, v0, rep, ca, cb, s_terms, acc, part);
             }
         }
-        tile_runs<RB, K + 1>(a, tile, v0, rep, s_recs, s_terms, gi, ra, rb, acc);
+        tile_runs<RB, K + 1, PT>(a, tile, v0, rep, s_recs, s_terms, gi, ra, rb, acc, part);
     }
 }
 
@@ -197,16 +210,32 @@ __device__ __forceinline__ void prefetch_l2(const void *p) {
 }
 
 // MINB = resident CTAs per SM the register allocation is held to (2: 128 registers, 3: 80 with spills)
-template <int MINB>
+// PT = per-term output (b200vqe_expectation(per_term), RDM): instead of the energy, every CTA leaves the signed pair
+// sums of each term over ITS tiles in term_partials[blockIdx.x][plan term] (per-warp accumulators in shared memory,
+// flushed at every batch switch; fixed order, no atomics); k_sum_term_partials adds the CTAs in order.
+template <int MINB, bool PT = false>
 __global__ void __launch_bounds__(kBlock, MINB)
 k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_bytes, const TileBatch *__restrict__ batches, int n_batches,
               unsigned long long tile_begin, unsigned long long tile_count, const TileRec *__restrict__ recs,
-              const TileTerm *__restrict__ terms, double *partials, unsigned *counter, double *out) {
+              const TileTerm *__restrict__ terms, double *partials, unsigned *counter, double *out,
+              double *term_partials = nullptr, int n_plan_terms = 0) {
     extern __shared__ __align__(16) unsigned char tile_raw[];
     double2 *tile = reinterpret_cast<double2 *>(tile_raw);
     __shared__ TileBatch sb;
     __shared__ __align__(16) int4 s_recs[2 * (kStageRecs + 1)];
     __shared__ __align__(16) double2 s_terms[kStageTerms];
+    __shared__ double s_part[PT ? kBlock / 32 : 1][PT ? kStageTerms : 1];
+    double *part = PT ? &s_part[threadIdx.x >> 5][0] : nullptr;
+    auto flush_terms = [&]() {      // PT: this CTA's sums of the finished batch -> global, warps added in order
+        __syncthreads();
+        const int n_t = sb.t_end - sb.t_begin;
+        for (int k = threadIdx.x; k < n_t; k += kBlock) {
+            double sum = 0.0;
+#pragma unroll
+            for (int wp = 0; wp < kBlock / 32; ++wp) sum += s_part[PT ? wp : 0][PT ? k : 0];
+            term_partials[(size_t)blockIdx.x * n_plan_terms + sb.t_begin + k] = sum;
+        }
+    };
     const unsigned v0 = threadIdx.x;
     const unsigned lo = v0 & ((1u << C) - 1u);
     double acc = 0.0;
@@ -222,6 +251,7 @@ k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_byte
         const int b = (int)(w / tile_count);
         const unsigned long long t = tile_begin + (w - (unsigned long long)b * tile_count);
         if (b != cur_b) {                       // uniform over the CTA
+            if (PT && cur_b >= 0) flush_terms();
             __syncthreads();
             if (threadIdx.x < 32)
                 reinterpret_cast<uint32_t *>(&sb)[threadIdx.x] = reinterpret_cast<const uint32_t *>(&batches[b])[threadIdx.x];
@@ -246,6 +276,11 @@ k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_byte
             if (threadIdx.x == 0) s_recs[2 * n_r] = make_int4(0, 0, 0xff << 16, 0);
             const double2 *tsrc = reinterpret_cast<const double2 *>(terms) + sb.t_begin;
             for (int i = threadIdx.x; i < n_t; i += kBlock) s_terms[i] = tsrc[i];
+            if (PT) {
+                for (int i = threadIdx.x; i < n_t; i += kBlock)
+#pragma unroll
+                    for (int wp = 0; wp < kBlock / 32; ++wp) s_part[PT ? wp : 0][PT ? i : 0] = 0.0;
+            }
             __syncthreads();
         }
         const unsigned rep = have_next ? rep_next : tile_rep(sb, (unsigned)t);   // high index (j >> C) has at most 32 bits
@@ -272,11 +307,26 @@ k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_byte
         }
         int gi = 0;
         int4 ra = s_recs[0], rb = s_recs[1];
-        tile_runs<4, 0>(a, tile, v0, rep, s_recs, s_terms, gi, ra, rb, acc);
+        tile_runs<4, 0, PT>(a, tile, v0, rep, s_recs, s_terms, gi, ra, rb, acc, part);
+    }
+    if (PT) {
+        if (cur_b >= 0) flush_terms();
+        return;
     }
     double v[1] = {acc};
     grid_reduce<1>(v, partials, counter, out, 1.0);
 }
+
+// out[k] = sum over CTAs (in order) of term_partials[cta][k]
+__global__ void __launch_bounds__(kBlock, 4)
+k_sum_term_partials(const double *__restrict__ term_partials, int n_cta, int n_plan_terms, double *__restrict__ out) {
+    const int k = blockIdx.x * kBlock + threadIdx.x;
+    if (k >= n_plan_terms) return;
+    double sum = 0.0;
+    for (int c = 0; c < n_cta; ++c) sum += term_partials[(size_t)c * n_plan_terms + k];
+    out[k] = sum;
+}
+
 
 // ---------------------------------------------------------------------------------------------
 // <psi|H|psi>, double-buffered: 2048-amplitude tiles (RB = 3, 8 amplitudes per thread, 32 KB), two tile buffers per CTA,
