@@ -98,7 +98,7 @@ static int ensure_slot(b200vqe_ctx *h, int slot) {
 static int ensure_gather(b200vqe_ctx *h) {
     if (h->world == 1 || h->gather) return 0;
     CK(cudaMalloc(&h->gather, (size_t)h->world * h->nloc * sizeof(double2)));
-    if (h->xbuf) { cudaStreamSynchronize(h->stream); cudaFree(h->xbuf); h->xbuf = nullptr; }   // gather now serves the pair exchanges too
+    if (h->xbuf) { cudaStreamSynchronize(h->stream); if (h->comm_stream) cudaStreamSynchronize(h->comm_stream); cudaFree(h->xbuf); h->xbuf = nullptr; }   // gather now serves the pair exchanges too
     return 0;
 }
 
@@ -133,17 +133,32 @@ static int wait_gather(b200vqe_ctx *h) {
 // Pairwise slab exchange for ansatz gates that flip a sharded qubit: this rank's slab goes to `peer` and the peer's
 // arrives in a staging buffer (grouped ncclSend/ncclRecv: the two directions of one NVLink pair run concurrently).
 // Every rank of a pair must call it; pairs are independent, so ranks outside the exchange simply do not call.
+static int exchange_bufs(b200vqe_ctx *h, double2 *bufs[2]) {
+    if (h->gather) { bufs[0] = h->gather; bufs[1] = h->gather + h->nloc; return 0; }
+    if (!h->xbuf) CK(cudaMalloc(&h->xbuf, 2 * h->nloc * sizeof(double2)));
+    bufs[0] = h->xbuf; bufs[1] = h->xbuf + h->nloc;
+    return 0;
+}
+
 static int exchange_with_peer(b200vqe_ctx *h, const double2 *src, int peer, const double2 **received) {
-    double2 *buf = h->gather;
-    if (!buf) {
-        if (!h->xbuf) CK(cudaMalloc(&h->xbuf, h->nloc * sizeof(double2)));
-        buf = h->xbuf;
-    }
+    double2 *bufs[2];
+    int rc = exchange_bufs(h, bufs);
+    if (rc) return rc;
     NK(g_nccl.GroupStart());
     NK(g_nccl.Send(src, h->nloc * 2, ncclDouble, peer, h->comm, h->stream));
-    NK(g_nccl.Recv(buf, h->nloc * 2, ncclDouble, peer, h->comm, h->stream));
+    NK(g_nccl.Recv(bufs[0], h->nloc * 2, ncclDouble, peer, h->comm, h->stream));
     NK(g_nccl.GroupEnd());
-    *received = buf;
+    *received = bufs[0];
+    return 0;
+}
+
+// The same exchange on the communication stream into staging buffer `which` (tile H psi: the slab of the next x_rank
+// class travels while the current class is computed).  The caller orders the streams with ev_free / ev_recv.
+static int exchange_async(b200vqe_ctx *h, const double2 *src, int peer, double2 *buf) {
+    NK(g_nccl.GroupStart());
+    NK(g_nccl.Send(src, h->nloc * 2, ncclDouble, peer, h->comm, h->comm_stream));
+    NK(g_nccl.Recv(buf, h->nloc * 2, ncclDouble, peer, h->comm, h->comm_stream));
+    NK(g_nccl.GroupEnd());
     return 0;
 }
 
@@ -203,9 +218,12 @@ static int create_common(int n_qubits, int device, int rank, int world, const ch
     if ((e = cudaMalloc(&h->d_out, sizeof(double) * kOutDoubles)) != cudaSuccess) return fail(cudaGetErrorString(e), B200VQE_ENOMEM);
     if ((e = cudaMallocHost(&h->h_out, sizeof(double) * kOutDoubles)) != cudaSuccess) return fail(cudaGetErrorString(e), B200VQE_ENOMEM);
     if (world > 1) {
-        if ((e = cudaStreamCreateWithFlags(&h->comm_stream, cudaStreamNonBlocking)) != cudaSuccess) return fail(cudaGetErrorString(e), B200VQE_ECUDA);
+        int prio_lo = 0, prio_hi = 0;      // the exchange kernels go first whenever CTAs of a compute launch retire
+        cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+        if ((e = cudaStreamCreateWithPriority(&h->comm_stream, cudaStreamNonBlocking, prio_hi)) != cudaSuccess) return fail(cudaGetErrorString(e), B200VQE_ECUDA);
         cudaEventCreateWithFlags(&h->ev_src_ready, cudaEventDisableTiming);
         cudaEventCreateWithFlags(&h->ev_gathered, cudaEventDisableTiming);
+        for (int i = 0; i < 2; ++i) { cudaEventCreateWithFlags(&h->ev_recv[i], cudaEventDisableTiming); cudaEventCreateWithFlags(&h->ev_free[i], cudaEventDisableTiming); }
         if (!g_nccl.load(g_err)) { delete h; return B200VQE_ECOMM; }
         ncclUniqueId u;
         memcpy(&u, id, 128);
@@ -228,7 +246,8 @@ int b200vqe_destroy(b200vqe_handle h) {
     if (!h) return 0;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
-    if (h->comm_stream) { cudaStreamSynchronize(h->comm_stream); cudaStreamDestroy(h->comm_stream); cudaEventDestroy(h->ev_src_ready); cudaEventDestroy(h->ev_gathered); }
+    if (h->comm_stream) { cudaStreamSynchronize(h->comm_stream); cudaStreamDestroy(h->comm_stream); cudaEventDestroy(h->ev_src_ready); cudaEventDestroy(h->ev_gathered);
+        for (int i = 0; i < 2; ++i) { cudaEventDestroy(h->ev_recv[i]); cudaEventDestroy(h->ev_free[i]); } }
     for (auto p : h->slots) if (p) cudaFree(p);
     if (h->gather) cudaFree(h->gather);
     if (h->xbuf) cudaFree(h->xbuf);
@@ -287,6 +306,12 @@ int b200vqe_set_option(b200vqe_handle h, const char *key, const char *value) {
         const int c = atoi(value);
         if (c < 2 || c > 8) FAIL(B200VQE_EINVAL, "tile-chunk-bits must be in [2, 8]");
         h->opt_tile_chunk_bits = c;
+        return 0;
+    }
+    if (k == "shard-exchange") {
+        if (v == "allgather" || v == "auto") h->opt_shard_exchange = 0;
+        else if (v == "pairwise") h->opt_shard_exchange = 1;
+        else FAIL(B200VQE_EINVAL, "shard-exchange must be auto, allgather or pairwise");
         return 0;
     }
     if (k == "tile-bits") {

@@ -76,7 +76,8 @@ struct b200vqe_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_t0 = nullptr, ev_t1 = nullptr;
     std::vector<double2 *> slots;
     double2 *gather = nullptr;          // [world][nloc] staging of the peers' shards
-    double2 *xbuf = nullptr;            // [nloc] staging of ONE peer's shard (ansatz gates on sharded qubits) when gather is absent
+    double2 *xbuf = nullptr;            // [2][nloc] staging of peer shards (pairwise exchanges: ansatz gates, tile H psi) when gather is absent
+    cudaEvent_t ev_recv[2] = {nullptr, nullptr}, ev_free[2] = {nullptr, nullptr};   // pipelined slab exchange of the tile H psi
     b200vqe::DeviceHam ham;
     double *partials = nullptr; unsigned *counter = nullptr;
     double *d_out = nullptr, *h_out = nullptr;
@@ -93,5 +94,6 @@ struct b200vqe_ctx {
     int opt_apply_engine = 0;           // same, for H psi
     int opt_tile_ctas = 2;              // resident CTAs per SM of the tile engine (2 or 3)
     int opt_tile_bits = 12;             // tile of the <psi|H|psi> engine: 12 = 4096 amplitudes single-buffered, 11 = 2048 double-buffered
+    int opt_shard_exchange = 0;         // tile H psi on a sharded register: 0 all-gather, 1 pairwise send/recv pipeline
     int opt_tile_chunk_bits = 3;        // C: contiguous amplitudes per chunk = 2^C (128 B at C = 3)
 };
