@@ -97,9 +97,10 @@ const char *b200vqe_last_error(b200vqe_handle h);
 /* String options in the manner of xacc::setOption(key, value) (e.g. task/tasks/DiagonalizeTask.cpp:15-30).
  *   "expect-engine"   = "auto" | "tile" | "stream"   which <psi|H|psi> kernel set_hamiltonian prepares
  *   "apply-engine"    = "auto" | "tile" | "stream"   the same for H psi (b200vqe_apply_h, b200vqe_lanczos_ground)
- *   "shard-exchange"  = "auto" | "allgather" | "pairwise"   how the tile H psi of a sharded register fetches peer slabs:
- *                                                    one ncclAllGather into `world` staging slabs (default, fastest measured) |
- *                                                    per-x_rank ncclSend/ncclRecv pairs pipelined through two staging slabs
+ *   "shard-exchange"  = "auto" | "allgather" | "needed" | "pairwise"   how the tile H psi of a sharded register fetches peer
+ *                                                    slabs: one ncclAllGather into `world` staging slabs (auto; fastest measured) |
+ *                                                    only the slabs the Hamiltonian's masks reach, one group of ncclSend/ncclRecv |
+ *                                                    per-x_rank send/recv pairs pipelined through two staging slabs (least memory)
  *   "tile-bits"       = "12" | "11"                  tile of the <psi|H|psi> engine: 4096 amplitudes single-buffered (two CTAs
  *                                                    per SM) | 2048 amplitudes double-buffered with cp.async (three CTAs per SM)
  *   "tile-ctas-per-sm" = "2" | "3"                   resident CTAs per SM of the tile engine's <psi|H|psi> kernel

@@ -64,6 +64,7 @@ def main():
     ap.add_argument("--max-iter", type=int, default=400)
     ap.add_argument("--out", default="")
     ap.add_argument("--apply-engine", default="auto", choices=["auto", "tile", "stream"])
+    ap.add_argument("--shard-exchange", default="auto", choices=["auto", "allgather", "needed", "pairwise"])
     args = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -90,6 +91,7 @@ def main():
 
     be = xb.Backend(n, device=local, rank=rank, world=world, comm_id=comm_id)
     be.set_option("apply-engine", args.apply_engine)
+    be.set_option("shard-exchange", args.shard_exchange)
     be.set_hamiltonian(xm, zm, cf)
     T, G = be.hamiltonian_stats()
     be.synchronize()
@@ -114,7 +116,7 @@ def main():
         eb, _ = po.ground_state_eigsh(xb_, zb_, packed(xb_, zb_, cb), m, tol=1e-13, apply=lambda v: co.apply(m, xb_, zb_, packed(xb_, zb_, cb), v))
         want = ea + eb
         N = 1 << n
-        line = {"config": f"synthetic {n}-qubit Pauli sum H_A(x)1 + 1(x)H_B, sharded Lanczos ground state", "n_qubits": n, "n_gpus": world, "apply_engine": args.apply_engine,
+        line = {"config": f"synthetic {n}-qubit Pauli sum H_A(x)1 + 1(x)H_B, sharded Lanczos ground state", "n_qubits": n, "n_gpus": world, "apply_engine": args.apply_engine, "shard_exchange": args.shard_exchange,
                 "n_terms": int(T), "n_xmask_groups": int(G), "state_GiB": N * 16 / 2**30, "eigenvalue": e0, "oracle_E0A_plus_E0B": want,
                 "rel_err": abs(e0 - want) / abs(want), "iterations": int(it), "ritz_residual": res, "seconds": dt,
                 "ms_per_iteration": 1e3 * dt / max(1, it), "hpsi_updates_per_s": T * N * it / dt, "gpu_launches": int(launches),

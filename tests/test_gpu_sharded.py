@@ -31,7 +31,7 @@ def _worker(rank, world, comm_id, n, T, seed, engine, lanczos, out_q):
     be = xb.Backend(n, device=rank, rank=rank, world=world, comm_id=comm_id)
     be.set_option("expect-engine", engine)
     be.set_option("apply-engine", engine)
-    be.set_option("shard-exchange", "pairwise" if seed % 2 else "allgather")     # both ways of fetching peer slabs (tile H psi)
+    be.set_option("shard-exchange", ("needed", "pairwise", "allgather")[seed % 3])     # both ways of fetching peer slabs (tile H psi)
     be.n_slots(2)
     be.set_hamiltonian(xm, zm, cf)
     lo, cnt = be.first, be.n_local

@@ -123,6 +123,28 @@ static int make_slabs(b200vqe_ctx *h, const double2 *src, Slabs &s) {
     return 0;
 }
 
+// The same, restricted to the peers whose slabs will be read (x_rank offsets present in the Hamiltonian): one NCCL group
+// of send/recv pairs, all running concurrently; NVLink bytes = 16 * 2^nl per offset instead of per peer.
+static int make_slabs_needed(b200vqe_ctx *h, const double2 *src, const std::vector<int> &x_ranks, Slabs &s) {
+    for (int i = 0; i < kMaxWorld; ++i) s.p[i] = nullptr;
+    s.p[h->rank] = src;
+    int rc = ensure_gather(h);
+    if (rc) return rc;
+    CK(cudaEventRecord(h->ev_src_ready, h->stream));
+    CK(cudaStreamWaitEvent(h->comm_stream, h->ev_src_ready, 0));
+    NK(g_nccl.GroupStart());
+    for (int c : x_ranks) {
+        const int peer = h->rank ^ c;
+        NK(g_nccl.Send(src, h->nloc * 2, ncclDouble, peer, h->comm, h->comm_stream));
+        NK(g_nccl.Recv(h->gather + (size_t)peer * h->nloc, h->nloc * 2, ncclDouble, peer, h->comm, h->comm_stream));
+        s.p[peer] = h->gather + (size_t)peer * h->nloc;
+    }
+    NK(g_nccl.GroupEnd());
+    CK(cudaEventRecord(h->ev_gathered, h->comm_stream));
+    h->gather_pending = true;
+    return 0;
+}
+
 static int wait_gather(b200vqe_ctx *h) {
     if (!h->gather_pending) return 0;
     CK(cudaStreamWaitEvent(h->stream, h->ev_gathered, 0));
@@ -309,9 +331,10 @@ int b200vqe_set_option(b200vqe_handle h, const char *key, const char *value) {
         return 0;
     }
     if (k == "shard-exchange") {
-        if (v == "allgather" || v == "auto") h->opt_shard_exchange = 0;
+        if (v == "auto" || v == "allgather") h->opt_shard_exchange = 0;
+        else if (v == "needed") h->opt_shard_exchange = 2;
         else if (v == "pairwise") h->opt_shard_exchange = 1;
-        else FAIL(B200VQE_EINVAL, "shard-exchange must be auto, allgather or pairwise");
+        else FAIL(B200VQE_EINVAL, "shard-exchange must be auto, allgather, needed or pairwise");
         return 0;
     }
     if (k == "tile-bits") {

@@ -94,6 +94,6 @@ struct b200vqe_ctx {
     int opt_apply_engine = 0;           // same, for H psi
     int opt_tile_ctas = 2;              // resident CTAs per SM of the tile engine (2 or 3)
     int opt_tile_bits = 12;             // tile of the <psi|H|psi> engine: 12 = 4096 amplitudes single-buffered, 11 = 2048 double-buffered
-    int opt_shard_exchange = 0;         // tile H psi on a sharded register: 0 all-gather, 1 pairwise send/recv pipeline
+    int opt_shard_exchange = 0;         // tile H psi on a sharded register: 0 all-gather (auto), 1 pairwise pipeline, 2 needed slabs only (one send/recv group)
     int opt_tile_chunk_bits = 3;        // C: contiguous amplitudes per chunk = 2^C (128 B at C = 3)
 };
