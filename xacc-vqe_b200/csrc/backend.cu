@@ -229,6 +229,18 @@ static int create_common(int n_qubits, int device, int rank, int world, const ch
     if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return fail(cudaGetErrorString(e), B200VQE_ECUDA);
     h->n_sm = prop.multiProcessorCount;
     h->smem_optin = (int)prop.sharedMemPerBlockOptin;
+    {   // opt-in shared memory of the tile kernels, per device (a process may hold handles on several)
+        const int tile = (int)(sizeof(double2) << kTileBits), two_small = (int)(2 * (sizeof(double2) << kTileBitsSmall));
+        cudaError_t ea = cudaSuccess;
+        auto set = [&](const void *f, int bytes) { if (ea == cudaSuccess) ea = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes); };
+        set((const void *)k_tile_expect<2, false>, tile);
+        set((const void *)k_tile_expect<3, false>, tile);
+        set((const void *)k_tile_expect<2, true>, tile);
+        set((const void *)k_tile_expect_db<3>, two_small);
+        set((const void *)k_tile_apply, tile);
+        set((const void *)k_sweep_small, tile);
+        if (ea != cudaSuccess) return fail(std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(ea), B200VQE_ECUDA);
+    }
     if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail(cudaGetErrorString(e), B200VQE_ECUDA);
     cudaEventCreate(&h->ev0);
     cudaEventCreate(&h->ev1);
