@@ -117,8 +117,9 @@ int b200vqe_set_hamiltonian(b200vqe_handle h, int64_t n_terms, const uint64_t *x
                             const uint64_t *zmask, const double *coef_re, const double *coef_im);
 int b200vqe_hamiltonian_stats(b200vqe_handle h, int64_t *n_terms, int64_t *n_groups);
 
-/* Host-only view of the tile-engine plan (see csrc/tile_plan.hpp) for a Hermitian term list: raw
- * TileBatch[128 B], TileGroup[16 B], TileTerm[16 B] records.  Call with NULL arrays for the counts. */
+/* Host-only view of the tile-engine plan (see csrc/tile_plan.hpp) for a Hermitian term list, exactly as
+ * b200vqe_set_hamiltonian builds it for <psi|H|psi> (batch capacities included): raw TileBatch[128 B],
+ * TileGroup[16 B], TileTerm[16 B] records.  tile_bits = 12 (4096-amplitude tiles) | 11.  NULL arrays: counts only. */
 int b200vqe_debug_tile_plan(int n_qubits, int chunk_bits, int tile_bits /* 12 | 11 */, int64_t n_terms, const uint64_t *xmask, const uint64_t *zmask,
                             const double *coef_re, const double *coef_im, int64_t *n_batches, int64_t *n_groups,
                             int64_t *n_plan_terms, void *batches, void *groups, void *terms);

@@ -1,16 +1,18 @@
-// Tile engine: <psi|H|psi> with several xmask groups evaluated per HBM read of the state.
-// See tile_plan.hpp for the decomposition.  One CTA = 256 threads owns one tile (a coset of the
-// batch's subspace: 4096 amplitudes, 64 KB) in shared memory; each thread also keeps its own 16
-// amplitudes in registers.  For every group of the batch a thread visits the 8 of its amplitudes
-// that are the "bit h clear" element of their pair {v, v^xv} (all 16 when the group has no register
-// bit), reads the partner from shared memory (one conflict-free LDS.128) and accumulates
-//     E += fe(j) Re w + go(j) Im w,   w = conj(psi[j^x]) psi[j],
-// fe/go being the signed coefficient sums of the group's even-/odd-nY terms at j.  The sign of a term
-// at register r factorises into a thread constant (one 64-bit POPC for the coset part, one 8-bit POPC
-// for the thread part) and a Walsh function of r, so a term costs one 8-point signed butterfly (7 DFMA)
-// per thread on top of the group's Re w / Im w products: about one DFMA per pair per term.
+// Tile engine: <psi|H|psi>, per-term <P_k> and H psi with several xmask groups evaluated per HBM read of the state.
+// See tile_plan.hpp for the decomposition.  One CTA = 256 threads owns one tile (a coset of the batch's subspace:
+// 4096 amplitudes, 64 KB) in shared memory; each thread also keeps its own 16 amplitudes in registers.  The batch's
+// groups arrive as RECORDS (TileRec: the even-nY or odd-nY terms of one group) sorted by key = (which, XR), XR being the
+// register part of the group's virtual flip mask, and every key has its own fully specialised loop: the partner of
+// register r is row r ^ XR of thread v0 ^ xt, an LDS.128 at an immediate offset.  <psi|H|psi> visits each pair
+// {v, v ^ xv} once (the 8 registers with bit msb(XR) clear; all 16 when XR = 0) and accumulates
+//     E += u s(j) Re w  |  u s(j) Im w,   w = conj(psi[j^x]) psi[j],
+// where the sign of a term at register r factorises into a thread constant (one POPC over the coset part xor the
+// thread part) and a Walsh function of r: one 8-point signed butterfly (7 DFMA) per term on top of the record's
+// Re w / Im w products.  H psi keeps 16 complex accumulators per thread and reads all 16 partner rows per record.
 //
-// HBM traffic: 16 B per amplitude per BATCH (>= kTileBits - C groups), no writes.
+// Kernels: k_tile_expect<MINB, PT> (single buffer; PT = per-term sums instead of the energy), k_tile_expect_db<3>
+// (2048-amplitude tiles, cp.async double buffering, opt-in), k_tile_apply (one launch per batch), k_sum_term_partials.
+// HBM traffic of <psi|H|psi>: 16 B per amplitude per BATCH (>= kTileBits - C groups), no writes.
 #pragma once
 #include "kernels.cuh"
 #include "tile_plan.hpp"

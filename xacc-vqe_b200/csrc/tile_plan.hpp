@@ -14,6 +14,12 @@
 // emits the device tables.  HBM traffic per group drops from 8 B (pair form of the streaming kernel)
 // to 16/d B per amplitude, d = groups per batch (>= M for unstructured Hamiltonians, far more for
 // molecular ones whose flip masks span a small space).
+//
+// Device tables: TileBatch (subspace basis, coset-representative masks, ranges), TileTerm (packed z parts + coefficient)
+// and, for the kernels, TileRec records (build_tile_records): one per (group, even/odd nY), sorted by the key that
+// selects the kernel's specialised loop.  TileGroup records remain for the natural-layout sweep kernel and the CPU
+// replay tests.  Plans for the kernels are built with per-batch capacities (kStageGroupsCap, kStageTerms) so that a
+// batch's records and terms always fit the kernels' shared-memory staging.
 #pragma once
 #include <algorithm>
 #include <cstdint>
