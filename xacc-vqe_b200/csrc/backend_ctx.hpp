@@ -44,6 +44,9 @@ struct DeviceHam {
     std::vector<double> tl_term_r;      // <P_k> = r_k * (signed pair sum): Re i^nY (even nY) | -Im i^nY (odd nY)
     // tile engine for H psi: one plan per x_rank class (which peer slab the partners live in), concatenated
     struct ApplyClass { int x_rank; int b_begin, b_end; };
+    struct ApplySrc { uint64_t x, z; double cre, cim; int ny; int64_t idx; };
+    bool ta_wanted = false, ta_built = false; int ta_chunk_bits = 3;
+    std::vector<ApplySrc> ta_src;   // terms kept on the host until the first H psi plans them
     std::vector<ApplyClass> ta_classes;
     int ta_C = 0, ta_M = 0, n_ta_batches = 0;
     TileBatch *ta_batches = nullptr; TileRec *ta_recs = nullptr; TileTerm *ta_terms = nullptr;
