@@ -179,3 +179,27 @@ def test_c_oracle_matches_numpy(n, T, seed):
         q = psi.copy()
         co.apply_gate(n, name, qs, th, q)
         assert np.abs(q - po.apply_gate(psi, name, qs, th)).max() < 1e-14
+
+
+@pytest.mark.parametrize("tr", ["jw", "bk"])
+def test_number_symmetry_sectors_tile_the_pinned_spectrum(golden, tr):
+    """diag-number-symmetry restatement (DiagonalizeTask.cpp:54-183) against the pinned dense branch: for H2 (n = 4, where
+    the reference's BK matrix matches its BK transformation) the n_e-electron sectors are invariant, so the literal
+    matrix (std::map quirk included) equals the compression P H P, the union of the sector spectra is the full spectrum,
+    and the 2-electron sector holds the reference's golden ground energy."""
+    op, n = po.compile_fermion_source(golden["h2_source"], tr)
+    full = np.linalg.eigvalsh(po.dense_matrix_reference(op, n))
+    parts = []
+    for ne in range(n + 1):
+        lit = po.number_subspace_matrix(op, n, ne, tr, literal=True)
+        proj = po.number_subspace_matrix(op, n, ne, tr, literal=False)
+        assert np.abs(lit - proj).max() < 1e-14
+        assert np.abs(lit - lit.conj().T).max() < 1e-14
+        assert lit.shape[0] == len(po.number_sector_strings(n, ne, tr)) == [1, 4, 6, 4, 1][ne]
+        parts.append(np.linalg.eigvalsh(lit))
+    assert np.abs(np.sort(np.concatenate(parts)) - full).max() < 1e-12
+    assert abs(po.diagonalize_number_symmetry(op, n, 2, tr) - golden["h2_ground_energy_exact"]) < 1e-13
+    # the BK re-encoding is a bijection on bit strings and keeps the vacuum
+    if tr == "bk":
+        allstr = [s for ne in range(n + 1) for s in po.number_sector_strings(n, ne, "bk")]
+        assert len(set(allstr)) == 1 << n and po.number_sector_strings(n, 0, "bk") == ["0" * n]
