@@ -167,10 +167,18 @@ typedef struct {
     int32_t want_vector; /* leave the Ritz vector in slot 0 */
     uint64_t seed;       /* start vector = normalised complex Gaussian(seed) unless use_slot0 */
     int32_t use_slot0;   /* start from the (non-zero) state already in slot 0 */
-    int32_t reserved;
+    int32_t reserved;    /* bit 0: resume the unfinished run kept in the handle (stopped at max_iter, or b200vqe_lanczos_load) */
 } b200vqe_lanczos_opts;
 int b200vqe_lanczos_ground(b200vqe_handle h, const b200vqe_lanczos_opts *opts, double *eigenvalue,
                            int32_t *iterations, double *residual);
+
+/* Checkpoint / resume of an unfinished Lanczos run (one file per rank: coefficients + the two live vectors of this
+ * rank's slab).  Counterpart, for this backend's long solve, of the reference's restart file
+ * (decorators/VQERestartDecorator.cpp:17-75).  A run that returns B200VQE_ENOCONV at max_iter keeps its recurrence in
+ * the handle (slots 1 and 2 must be left alone); save it, later: create + set_hamiltonian + load + lanczos_ground with
+ * reserved = 1 and a larger max_iter continues exactly where it stopped. */
+int b200vqe_lanczos_save(b200vqe_handle h, const char *path);
+int b200vqe_lanczos_load(b200vqe_handle h, const char *path);
 
 /* Particle-number sector (replaces the diag-number-symmetry branch, task/tasks/DiagonalizeTask.cpp:54-183, options
  * "diag-number-symmetry" + "n-electrons" + "fermion-transformation"): while set, b200vqe_lanczos_ground diagonalises

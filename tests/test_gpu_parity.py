@@ -411,3 +411,35 @@ def test_per_term_expectations_on_the_tile_engine(xb, n, T, seed, structured):
         got[engine] = per
         be.close()
     assert np.abs(got["tile"] - got["stream"]).max() < 1e-11
+
+
+def test_lanczos_checkpoint_and_resume(xb, tmp_path):
+    """A run cut at max_iter is saved, reloaded into a NEW handle and continued: same eigenvalue, same total number of
+    steps as the uninterrupted run (the recurrence is deterministic), also when continued in place without a file."""
+    n, T, seed = 14, 60, 55
+    xm, zm, cf = random_hamiltonian(n, T, seed)
+    be = xb.Backend(n)
+    be.set_hamiltonian(xm, zm, cf)
+    e_ref, it_ref, _ = be.lanczos_ground(tol=1e-11, max_iter=2000, seed=seed)
+    assert it_ref > 24
+    with pytest.raises(xb.B200Error):
+        be.lanczos_ground(tol=1e-11, max_iter=16, seed=seed)            # stops unconverged, keeps the recurrence
+    path = str(tmp_path / "lanczos.ckpt")
+    be.lanczos_save(path)
+    e1, it1, _ = be.lanczos_ground(tol=1e-11, max_iter=2000, resume=True)      # continue in place
+    assert it1 == it_ref and abs(e1 - e_ref) < 1e-12 * max(1.0, abs(e_ref))
+    with pytest.raises(xb.B200Error):
+        be.lanczos_ground(tol=1e-11, max_iter=2000, resume=True)       # finished: nothing left to resume
+    be.close()
+    be2 = xb.Backend(n)
+    be2.set_hamiltonian(xm, zm, cf)
+    with pytest.raises(xb.B200Error):
+        be2.lanczos_ground(tol=1e-11, max_iter=2000, resume=True)      # nothing loaded yet
+    be2.lanczos_load(path)
+    e2, it2, _ = be2.lanczos_ground(tol=1e-11, max_iter=2000, resume=True)
+    assert it2 == it_ref and abs(e2 - e_ref) < 1e-12 * max(1.0, abs(e_ref))
+    be3 = xb.Backend(n + 1)
+    with pytest.raises(xb.B200Error):
+        be3.lanczos_load(path)                                          # wrong register size
+    be3.close()
+    be2.close()

@@ -314,11 +314,18 @@ class Backend:
         return complex(a[0], a[1]) if want_alpha else None
 
     def lanczos_ground(self, tol: float = 1e-10, max_iter: int = 1000, want_vector: bool = False, seed: int = 1,
-                       use_slot0: bool = False):
-        o = LanczosOpts(tol, max_iter, int(want_vector), seed, int(use_slot0), 0)
+                       use_slot0: bool = False, resume: bool = False):
+        """resume=True continues the unfinished run kept in the handle (stopped at max_iter, or lanczos_load)."""
+        o = LanczosOpts(tol, max_iter, int(want_vector), seed, int(use_slot0), int(resume))
         ev, it, res = C.c_double(), C.c_int32(), C.c_double()
         self._ck(lib().b200vqe_lanczos_ground(self.h, C.byref(o), C.byref(ev), C.byref(it), C.byref(res)))
         return ev.value, it.value, res.value
+
+    def lanczos_save(self, path: str):
+        self._ck(lib().b200vqe_lanczos_save(self.h, os.fsencode(path)))
+
+    def lanczos_load(self, path: str):
+        self._ck(lib().b200vqe_lanczos_load(self.h, os.fsencode(path)))
 
     def set_number_sector(self, n_electrons: int, transformation: str = "jw"):
         """diag-number-symmetry (task/tasks/DiagonalizeTask.cpp:54-183): Lanczos runs on P H P; n_electrons < 0 clears."""

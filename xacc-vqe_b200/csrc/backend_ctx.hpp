@@ -85,6 +85,8 @@ struct b200vqe_ctx {
     double *partials = nullptr; unsigned *counter = nullptr;
     double *d_out = nullptr, *h_out = nullptr;
     double *d_alpha = nullptr, *d_norm = nullptr, *d_ritz = nullptr; int lanczos_cap = 0;
+    // Lanczos recurrence kept between calls (resume / checkpoint): alpha_0..alpha_{m-1}, beta_1..beta_m, W_m and W_{m-1} in slots 1, 2
+    std::vector<double> lz_a, lz_b; int lz_m = -1;
     double *d_term_partials = nullptr, *d_term_out = nullptr; size_t term_partials_cap = 0, term_out_cap = 0;
     ncclComm_t comm = nullptr;
     std::string err;
