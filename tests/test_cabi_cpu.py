@@ -124,3 +124,20 @@ def test_number_sector_rows_bit_exact(n):
     else:
         for j in want:
             assert sum(bin(r & j).count("1") & 1 for r in rows) == ne
+
+
+def test_header_is_plain_c_and_example_links(tmp_path):
+    """include/b200vqe.h compiles as strict C99 (no C++ or torch types at the boundary), and the plain-C example links
+    against libb200vqe.so; its host part (FermionCompiler text -> JW -> packing) runs anywhere, the device part needs a GPU."""
+    import subprocess
+    lib_dir = os.path.join(ROOT, "xacc-vqe_b200")
+    exe = str(tmp_path / "h2")
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "examples", "h2_ground_state.c"), "-L", lib_dir, "-lb200vqe",
+                           "-Wl,-rpath," + lib_dir, "-o", exe])
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert "H2: 4 qubits, 15 Pauli terms" in r.stdout
+    if _has_gpu():
+        assert r.returncode == 0 and "E0 = -1.13727042206" in r.stdout
+    else:
+        assert r.returncode == 1 and "no CPU fallback" in r.stdout
