@@ -320,14 +320,28 @@ def run_gpu(args):
             "kernel": ("k_tile_apply" if tile else "k_apply<8,true>") if apply_op else (("k_tile_expect_db<3>" if args.tile_bits == 11 else "k_tile_expect<2>") if tile else "k_expect_energy<8,true>"),
             "peak_source": peak_src,
             "launches_per_step": int(launches // max(1, args.steps)),
-            "note": ("achieved = ALGORITHMIC bytes 16 B x 2^n_local x G (SURVEY.md 8d) / CUDA-event time of the step's single "
+            "note": ("achieved = ALGORITHMIC bytes 16 B x 2^n_local x (G + 1) (SURVEY.md 8d: G partner reads + one write) / CUDA-event "
+                     "time of the step's H.psi launch(es); the tile engine reads src once and read-modify-writes dst once per "
+                     "BATCH of xmask groups (48 B per amplitude per batch), so frac > 1 is expected") if apply_op else
+                    ("achieved = ALGORITHMIC bytes 16 B x 2^n_local x G (SURVEY.md 8d) / CUDA-event time of the step's single "
                      "k_tile_expect launch. The tile engine evaluates >= 9 xmask groups per HBM read of the state (GF(2)-subspace "
                      "tiles in shared memory), so its DRAM traffic is ~16 B x 2^n x n_batches and frac > 1 is expected; the "
-                     "kernel is bound by shared-memory bandwidth and issue, see DESIGN.md") if tile else
-                    ("achieved = ALGORITHMIC bytes 16 B x 2^n_local x (G + 1) (SURVEY.md 8d: G partner reads + one write) / CUDA-event "
-                     "time of the step's H.psi launch(es)") if apply_op else
+                     "kernel is bound by shared-memory bandwidth (see 'shared_memory' and DESIGN.md 3.1)") if tile else
                     ("achieved = 16 B x 2^n_local x G per step / CUDA-event time of the step's k_expect_energy launches "
                      "(one launch per xmask bucket); the pair form reads each pair once, so DRAM traffic is about half the model")}
+    clocks = clk.summary()
+    if tile and not apply_op and args.op == "expect" and traffic:
+        # the two physical bounds of the tile kernel next to the algorithmic one: measured DRAM bytes of this launch and the
+        # shared-memory bytes its design cannot avoid (16 B partner read per pair per group, 17/16 for the all-registers class,
+        # plus the tile fill of every batch) against 128 B/clk/SM at the SM clock sampled during the run
+        n_batches = traffic / (16.0 * be.n_local)
+        smem_bytes = 16.0 * (G * (be.n_local / 2) * (17.0 / 16.0) + n_batches * be.n_local)
+        smem_peak = torch.cuda.get_device_properties(local_rank).multi_processor_count * 128.0 * float(clocks.get("sm_mhz") or 0) * 1e6 / 1e9
+        roof["dram"] = {"achieved": traffic / (k_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "frac": traffic / (k_ms * 1e-3) / 1e9 / peak}
+        if smem_peak > 0:
+            roof["shared_memory"] = {"achieved": smem_bytes / (k_ms * 1e-3) / 1e9, "peak": smem_peak, "unit": "GB/s",
+                                     "frac": smem_bytes / (k_ms * 1e-3) / 1e9 / smem_peak,
+                                     "note": "design floor of shared-memory bytes / (SMs x 128 B/clk x sampled SM clock)"}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
@@ -335,7 +349,7 @@ def run_gpu(args):
                        "n_qubits": n, "n_terms": int(Tn), "n_xmask_groups": int(G), "amplitudes_per_gpu": int(be.n_local),
                        "parallelism": f"state sharded over {world} GPU(s) by high index bits",
                        "l2": "inputs larger than L2 (4.3 GB state per GPU vs 126 MB)"},
-            "roofline": roof, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk.summary(),
+            "roofline": roof, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
             "check": {"product_state_rel_err": check_rel, "energy": [e.real, e.imag]}}
     if world == 1 and not args.no_cpu:
         base, _, _ = cpu_baseline(n, xm, zm, cf, args.cpu_terms)
