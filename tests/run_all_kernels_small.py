@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Small invocation of every tile-engine kernel, checked against the CPU oracle as it goes (verification script, not
-product code).  Written for `compute-sanitizer --tool racecheck|memcheck python tools/sanitize_small.py` (SURVEY.md
+product code).  Written for `compute-sanitizer --tool racecheck|memcheck python tests/run_all_kernels_small.py` (SURVEY.md
 section 5); compute-sanitizer is closed on this pool's boxes, so in round 1 it only ran bare."""
 import os
 import sys
@@ -52,7 +52,7 @@ def main():
         be.apply_pauli_rotations(x, z, ic * th[v][pa])                          # k_pauli_rotation
         assert abs(be.expectation().real - es[v]) < 1e-12 * np.abs(cs).sum()
     be.close()
-    print("sanitize_small ok")
+    print("all kernels small: ok")
 
 
 if __name__ == "__main__":
