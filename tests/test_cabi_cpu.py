@@ -141,3 +141,38 @@ def test_header_is_plain_c_and_example_links(tmp_path):
         assert r.returncode == 0 and "E0 = -1.13727042206" in r.stdout
     else:
         assert r.returncode == 1 and "no CPU fallback" in r.stdout
+
+
+def _random_fermion_source(n_sites, n_terms, seed):
+    """Seeded FermionCompiler text (compiler/FermionCompiler.cpp:62-103): a constant, then terms of 2 or 4 ladder operators
+    '<coeff> <site> <1|0> ...' with repeated sites and both orders; coefficients are real, as the reference's std::stod
+    parse requires (:85-87)."""
+    rng = np.random.default_rng(seed)
+    lines = ["__qpu__ k() {", repr(float(rng.normal()))]
+    for _ in range(n_terms):
+        k = 2 if rng.random() < 0.5 else 4
+        sites = rng.integers(0, n_sites, k)
+        dags = rng.integers(0, 2, k)
+        lines.append(repr(float(rng.normal())) + " " + " ".join("%d %d" % (s, d) for s, d in zip(sites, dags)))
+    lines.append("}")
+    return "\n".join(lines)
+
+
+@pytest.mark.parametrize("n_sites,n_terms,seed", [(3, 12, 1), (5, 30, 2), (6, 40, 3), (7, 25, 4), (10, 60, 5), (13, 40, 6)])
+@pytest.mark.parametrize("tr", ["jw", "bk"])
+def test_front_end_random_sources_bit_exact(n_sites, n_terms, seed, tr):
+    """C++ front end against the oracle on seeded random sources, including register sizes that are not powers of two
+    (the Fenwick-tree BK of bk/Fenwick.hpp:83-176): identical masks, identical IEEE doubles, identical term ids."""
+    src = _random_fermion_source(n_sites, n_terms, seed)
+    oop, n = po.compile_fermion_source(src, tr, n_sites)
+    oxm, ozm, ocf, oids = po.pack_terms(oop)
+    op = xb.OpHandle.from_fermion_source(src, tr, n_sites)
+    xm, zm, cf = op.pack()
+    assert op.n_terms() == len(oxm)
+    assert np.array_equal(xm, oxm) and np.array_equal(zm, ozm)
+    assert np.array_equal(cf.view(np.float64), ocf.view(np.float64))
+    assert op.term_ids() == oids
+    # text round trip through the PauliOperator string form keeps every bit of every coefficient
+    again = xb.OpHandle.from_string(op.to_string())
+    xm2, zm2, cf2 = again.pack()
+    assert np.array_equal(xm2, xm) and np.array_equal(zm2, zm) and np.array_equal(cf2.view(np.float64), cf.view(np.float64))
