@@ -129,6 +129,13 @@ int b200vqe_debug_tile_plan(int n_qubits, int chunk_bits, int tile_bits /* 12 | 
 int b200vqe_debug_tile_records(int n_qubits, int chunk_bits, int tile_bits, int64_t n_terms, const uint64_t *xmask, const uint64_t *zmask,
                                const double *coef_re, const double *coef_im, int64_t *n_records, void *records);
 
+/* Host-only: the tile-engine plan of H psi for shard `rank` of `world` (csrc/tile_plan.hpp records, one plan per x_rank
+ * class = which peer slab the partners are read from; classes[3k..3k+2] = x_rank, first batch, end batch).  NULL arrays: counts. */
+int b200vqe_debug_apply_plan(int n_qubits, int rank, int world, int chunk_bits, int64_t n_terms, const uint64_t *xmask,
+                             const uint64_t *zmask, const double *coef_re, const double *coef_im, int64_t *n_batches,
+                             int64_t *n_records, int64_t *n_plan_terms, int64_t *n_classes, void *batches, void *records,
+                             void *terms, int32_t *classes);
+
 /* Host-only: slab and tile-engine share of `rank` in a register sharded over `world` ranks (what
  * b200vqe_create_sharded / b200vqe_expectation use).  No device needed. */
 int b200vqe_debug_shard_layout(int n_qubits, int rank, int world, int tile_bits, uint64_t *n_local, uint64_t *first_index,

@@ -1,7 +1,8 @@
 """N > 1 host logic on the CPU, world_size 2 over gloo: the shard layout the library uses (slabs, tile shares), the
 unique-id broadcast bench.py performs, and the sharded <psi|H|psi> decomposition itself -- each rank replays only ITS
 share of the tile-engine plan (numpy replay of k_tile_expect) and the gloo all_reduce of the partial sums must equal the
-oracle, exactly as ncclAllReduce combines the per-GPU partials on the device path."""
+oracle, exactly as ncclAllReduce combines the per-GPU partials on the device path; and the sharded H psi: each rank replays
+its own apply plan (partners from the peer's slab for x_rank != 0) and the all-gathered slabs must equal the oracle's H psi."""
 import ctypes as C
 import os
 import sys
@@ -59,6 +60,20 @@ def _worker(rank, world, port, n, T, seed, q):
     # norm^2 of the sharded state: local slab sums, all-reduced (b200vqe_state_norm2 on a sharded handle)
     nrm = torch.tensor([float(np.vdot(psi[first:first + nloc], psi[first:first + nloc]).real)], dtype=torch.float64)
     dist.all_reduce(nrm, op=dist.ReduceOp.SUM)
+    # H psi: this rank's plan (x_rank classes over the peers' slabs) gives its slab; all_gather assembles the vector, and
+    # the Lanczos scalar alpha = <psi|H psi> is the all-reduced sum of the per-slab inner products (ncclAllReduce on the device)
+    import c_oracle as co
+    Ba, Ra, Ta, classes = tp.get_apply_plan(n, 3, xm, zm, cf, rank, world)
+    mine = tp.replay_apply(n, 3, Ba, Ra, Ta, classes, psi, rank, world)
+    slabs = [torch.zeros(nloc, dtype=torch.complex128) for _ in range(world)]
+    dist.all_gather(slabs, torch.from_numpy(mine))
+    hpsi = torch.cat(slabs).numpy()
+    want = co.apply(n, xm, zm, cf, psi)
+    assert np.abs(hpsi - want).max() < 1e-12 * float(np.abs(cf).sum())
+    alpha = torch.tensor([float(np.vdot(psi[first:first + nloc], mine).real)], dtype=torch.float64)
+    dist.all_reduce(alpha, op=dist.ReduceOp.SUM)
+    assert abs(alpha.item() - float(np.vdot(psi, want).real)) < 1e-11 * float(np.abs(cf).sum())
+    assert any(int(c[0]) != 0 for c in classes)               # a class that reads the peer's slab exists
     q.put((rank, [t.tolist() for t in lays], float(tot.item()), part, float(nrm.item())))
     dist.barrier()
     dist.destroy_process_group()

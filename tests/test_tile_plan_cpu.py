@@ -158,6 +158,67 @@ def replay_records(n, c, B, R, T, psi, tb=12, tile_begin=0, tile_count=None):
     return total
 
 
+def get_apply_plan(n, c, xm, zm, cf, rank=0, world=1):
+    """b200vqe_debug_apply_plan: the H psi tables of one shard, as ensure_apply_plan uploads them."""
+    lib = xb.capi.lib()
+    xm = np.ascontiguousarray(xm, np.uint64)
+    zm = np.ascontiguousarray(zm, np.uint64)
+    cr, ci = np.ascontiguousarray(cf.real), np.ascontiguousarray(cf.imag)
+    nb, nr, nt, nc = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int64()
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)
+    args = (C.c_int(n), C.c_int(rank), C.c_int(world), C.c_int(c), C.c_int64(len(xm)), vp(xm), vp(zm), vp(cr), vp(ci),
+            C.byref(nb), C.byref(nr), C.byref(nt), C.byref(nc))
+    assert lib.b200vqe_debug_apply_plan(*args, None, None, None, None) == 0
+    B, R, T = np.zeros(nb.value, BATCH_DT), np.zeros(nr.value, REC_DT), np.zeros(nt.value, TERM_DT)
+    cls = np.zeros(3 * nc.value, np.int32)
+    assert lib.b200vqe_debug_apply_plan(*args, vp(B), vp(R), vp(T), vp(cls)) == 0
+    return B, R, T, cls.reshape(-1, 3)
+
+
+def replay_apply(n, c, B, R, T, classes, psi, rank=0, world=1):
+    """What k_tile_apply computes for shard `rank`: for every x_rank class the partners come from the slab of rank ^ x_rank;
+    per record, output v of a tile receives f(v) * src[v ^ xv] (times i for odd nY), f(v) = sum_e u_e (-1)^sign_e(v) with the
+    sign evaluated at the thread's OWN index.  Returns the local slab of H psi."""
+    nl = n - int(np.log2(world))
+    nloc = 1 << nl
+    M = TILE_BITS - c
+    v = np.arange(1 << TILE_BITS, dtype=np.uint64)
+    mu = v >> np.uint64(c)
+    lo = v & np.uint64((1 << c) - 1)
+    out = np.zeros(nloc, complex)
+    for x_rank, b0, b1 in classes:
+        peer = rank ^ int(x_rank)
+        slab = psi[peer * nloc:(peer + 1) * nloc]
+        for b in B[b0:b1]:
+            recs = R[b["r_begin"]:b["r_end"]]
+            assert len(recs) <= STAGE_RECS and b["t_end"] - b["t_begin"] <= STAGE_TERMS
+            assert list(recs["key"]) == sorted(recs["key"])
+            combo = np.zeros(1 << TILE_BITS, np.uint64)
+            for i in range(M):
+                combo ^= np.where((mu >> np.uint64(i)) & np.uint64(1), np.uint64(b["basis"][i]), np.uint64(0)).astype(np.uint64)
+            for t in range(1 << (nl - TILE_BITS)):
+                rep = 0
+                for i in range(11):
+                    rep |= (t & int(b["seg"][i])) << i
+                j = (((np.uint64(rep) ^ combo) << np.uint64(c)) | lo).astype(np.int64)
+                tile = slab[j]
+                acc = np.zeros(1 << TILE_BITS, complex)
+                for rec in recs:
+                    key, xv = int(rec["key"]), int(rec["xv"])
+                    which, xr = key >> 4, ((key & 15) + 1) & 15
+                    assert xr == xv >> 8
+                    f = np.zeros(1 << TILE_BITS)
+                    for k in range(int(rec["kb"]), int(rec["kb"] + rec["count"])):
+                        packed, u = int(T[k]["packed"]), float(T[k]["u"])
+                        par = (bin(rep & packed & 0xFFFFFFFF).count("1") & 1) ^ parity(v & np.uint64(0xFF) & np.uint64((packed >> 32) & 0xFF))
+                        word = (packed >> 48) & 0xFFFF                    # sign word: bit r = parity(r & zr)
+                        sr = (np.uint64(word) >> (v >> np.uint64(8))) & np.uint64(1)
+                        f += (1.0 - 2.0 * (par ^ sr.astype(np.int64))) * u
+                    acc += (f if which == 0 else 1j * f) * tile[(v ^ np.uint64(xv)).astype(np.int64)]
+                out[j] += acc
+    return out
+
+
 def random_hamiltonian(n, T, seed, weights=None):
     rng = np.random.default_rng(seed)
     pa = rng.integers(0, 4, size=(T, n)) if weights is None else rng.choice(4, size=(T, n), p=weights)
@@ -199,6 +260,27 @@ def test_plan_replay_matches_oracle(n, T, c, seed, weights):
         B2, G2, T2 = get_plan(n, c, xm, zm, cf, tb=11)
         e2 = replay_records(n, c, B2, get_records(n, c, xm, zm, cf, tb=11), T2, psi, tb=11)
         assert abs(e2 - eo.real) < 1e-11 * np.abs(cf).sum()
+
+
+@pytest.mark.parametrize("n,T,c,seed,world,weights", [(13, 40, 3, 21, 1, None), (14, 60, 2, 22, 2, None), (14, 50, 3, 23, 4, None),
+                                                     (13, 300, 3, 24, 2, (0.6, 0.05, 0.05, 0.3))])
+def test_apply_plan_replay_matches_oracle(n, T, c, seed, world, weights):
+    """Host logic of the sharded tile H psi on the CPU: every rank's plan (x_rank classes, rank-bit signs folded into the
+    coefficients, records) replayed in numpy over the peers' slabs gives that rank's slab of the oracle's H psi."""
+    xm, zm, cf = random_hamiltonian(n, T, seed, weights)
+    xm = np.concatenate([xm, np.zeros(1, np.uint64)])        # + the identity term (kept in the H psi tables)
+    zm = np.concatenate([zm, np.zeros(1, np.uint64)])
+    cf = np.concatenate([cf, np.array([0.37 + 0j])])
+    rng = np.random.default_rng(seed + 50)
+    psi = rng.normal(size=1 << n) + 1j * rng.normal(size=1 << n)
+    psi /= np.linalg.norm(psi)
+    want = co.apply(n, xm, zm, cf, psi)
+    nloc = (1 << n) // world
+    for rank in range(world):
+        B, R, Tt, classes = get_apply_plan(n, c, xm, zm, cf, rank, world)
+        assert len(Tt) == len(xm) and sorted(set(classes[:, 0])) == list(classes[:, 0])
+        got = replay_apply(n, c, B, R, Tt, classes, psi, rank, world)
+        assert np.abs(got - want[rank * nloc:(rank + 1) * nloc]).max() < 1e-12 * np.abs(cf).sum()
 
 
 def test_batch_capacity_splits_large_groups_and_batches():
