@@ -105,6 +105,8 @@ const char *b200vqe_last_error(b200vqe_handle h);
  *                                                    per SM) | 2048 amplitudes double-buffered with cp.async (three CTAs per SM)
  *   "tile-ctas-per-sm" = "2" | "3"                   resident CTAs per SM of the tile engine's <psi|H|psi> kernel
  *   "tile-chunk-bits" = "2".."8"                     contiguous amplitudes per HBM chunk of the tile engine
+ *   "tile-planner"    = "2" | "1"                    tile planner: collision-greedy subspaces + register subspace spanned by
+ *                                                    member masks (pure-register records) | the first version
  * Options take effect at the next b200vqe_set_hamiltonian. */
 int b200vqe_set_option(b200vqe_handle h, const char *key, const char *value);
 int b200vqe_n_slots(b200vqe_handle h, int n_slots);   /* number of resident statevectors (default 1) */
@@ -118,11 +120,14 @@ int b200vqe_set_hamiltonian(b200vqe_handle h, int64_t n_terms, const uint64_t *x
 int b200vqe_hamiltonian_stats(b200vqe_handle h, int64_t *n_terms, int64_t *n_groups);
 
 /* Host-only view of the tile-engine plan (see csrc/tile_plan.hpp) for a Hermitian term list, exactly as
- * b200vqe_set_hamiltonian builds it for <psi|H|psi> (batch capacities included): raw TileBatch[128 B],
+ * b200vqe_set_hamiltonian builds it for <psi|H|psi> (batch capacities included): raw TileBatch[160 B],
  * TileGroup[16 B], TileTerm[16 B] records.  tile_bits = 12 (4096-amplitude tiles) | 11.  NULL arrays: counts only. */
 int b200vqe_debug_tile_plan(int n_qubits, int chunk_bits, int tile_bits /* 12 | 11 */, int64_t n_terms, const uint64_t *xmask, const uint64_t *zmask,
                             const double *coef_re, const double *coef_im, int64_t *n_batches, int64_t *n_groups,
                             int64_t *n_plan_terms, void *batches, void *groups, void *terms);
+
+/* Host-only: planner version (the "tile-planner" option) the b200vqe_debug_* plan functions use; default 2. */
+int b200vqe_debug_set_planner(int planner);
 
 /* Host-only: the TileRec[32 B] records (csrc/tile_plan.hpp) the <psi|H|psi> kernel walks for that plan; the r_begin / r_end
  * fields of a TileBatch index them.  Call with NULL for the count. */

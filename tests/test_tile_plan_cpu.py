@@ -12,7 +12,8 @@ import xaccvqe_b200 as xb
 
 TILE_BITS = 12
 BATCH_DT = np.dtype([("basis", "<u4", 10), ("seg", "<u4", 11), ("g_begin", "<i4"), ("g_end", "<i4"),
-                     ("t_begin", "<i4"), ("t_end", "<i4"), ("cls_end", "<i4", 5), ("r_begin", "<i4"), ("r_end", "<i4")])
+                     ("t_begin", "<i4"), ("t_end", "<i4"), ("cls_end", "<i4", 5), ("r_begin", "<i4"), ("r_end", "<i4"),
+                     ("lam", "<u4", 4), ("pad", "<u4", 4)])
 GROUP_DT = np.dtype([("kb", "<u4"), ("n_even", "<u4"), ("n_odd", "<u4"), ("xv", "<u2"), ("hsel", "<i2")])
 TERM_DT = np.dtype([("packed", "<u8"), ("u", "<f8")])
 REC_DT = np.dtype([("kb", "<u4"), ("count", "<u4"), ("xv", "<u2"), ("key", "u1"), ("pad0", "u1"), ("pad1", "<u4"),
@@ -45,7 +46,7 @@ def get_plan(n, c, xm, zm, cf, tb=12):
     args = (C.c_int(n), C.c_int(c), C.c_int(tb), C.c_int64(len(xm)), vp(xm), vp(zm), vp(cr), vp(ci), C.byref(nb), C.byref(ng), C.byref(nt))
     assert lib.b200vqe_debug_tile_plan(*args, None, None, None) == 0
     B, G, T = np.zeros(nb.value, BATCH_DT), np.zeros(ng.value, GROUP_DT), np.zeros(nt.value, TERM_DT)
-    assert BATCH_DT.itemsize == 128 and GROUP_DT.itemsize == 16 and TERM_DT.itemsize == 16
+    assert BATCH_DT.itemsize == 160 and GROUP_DT.itemsize == 16 and TERM_DT.itemsize == 16
     assert lib.b200vqe_debug_tile_plan(*args, vp(B), vp(G), vp(T)) == 0
     return B, G, T
 
@@ -55,6 +56,15 @@ def parity(a):
     for s in (32, 16, 8, 4, 2, 1):
         a = a ^ (a >> np.uint64(s))
     return (a & np.uint64(1)).astype(np.int64)
+
+
+def shear(b, v, rb=4):
+    """Lambda(register of v): register r of a thread holds the amplitude whose low index bits are lo ^ Lambda(r) (TileBatch.lam)."""
+    r = v >> np.uint64(8)
+    out = np.zeros(len(v), np.uint64)
+    for k in range(rb):
+        out ^= np.where((r >> np.uint64(k)) & np.uint64(1), np.uint64(b["lam"][k]), np.uint64(0)).astype(np.uint64)
+    return out
 
 
 def replay(n, c, B, G, T, psi, tile_begin=0, tile_count=None):
@@ -74,7 +84,7 @@ def replay(n, c, B, G, T, psi, tile_begin=0, tile_count=None):
             rep = 0
             for i in range(11):
                 rep |= (t & int(b["seg"][i])) << i
-            j = ((np.uint64(rep) ^ combo) << np.uint64(c)) | lo
+            j = ((np.uint64(rep) ^ combo) << np.uint64(c)) | (lo ^ shear(b, v))
             tile = psi[j.astype(np.int64)]
             cls = [int(g["hsel"]) for g in G[b["g_begin"]:b["g_end"]]]
             want_cls = sum(([c] * (int(e) - (int(b["cls_end"][i - 1]) if i else 0)) for i, (c, e) in
@@ -131,12 +141,12 @@ def replay_records(n, c, B, R, T, psi, tb=12, tile_begin=0, tile_count=None):
             rep = 0
             for i in range(11):
                 rep |= (t & int(b["seg"][i])) << i
-            j = ((np.uint64(rep) ^ combo) << np.uint64(c)) | lo
+            j = ((np.uint64(rep) ^ combo) << np.uint64(c)) | (lo ^ shear(b, v, tb - 8))
             tile = psi[j.astype(np.int64)]
             for rec in recs:
                 key, xv = int(rec["key"]), int(rec["xv"])
-                which, xr = key >> 4, ((key & 15) + 1) & 15
-                assert xr == xv >> 8 and rec["count"] >= 1
+                which, xr, pure = (key >> 4) & 1, ((key & 15) + 1) & 15, key >> 5
+                assert xr == xv >> 8 and rec["count"] >= 1 and pure == int((xv & 0xFF) == 0)
                 assert b["t_begin"] <= rec["kb"] and rec["kb"] + rec["count"] <= b["t_end"]
                 assert T[rec["kb"]]["packed"] == rec["packed0"] and T[rec["kb"]]["u"] == rec["u0"]
                 r = v >> np.uint64(8)
@@ -206,7 +216,7 @@ def replay_apply(n, c, B, R, T, classes, psi, rank=0, world=1):
                 for rec in recs:
                     key, xv = int(rec["key"]), int(rec["xv"])
                     which, xr = key >> 4, ((key & 15) + 1) & 15
-                    assert xr == xv >> 8
+                    assert xr == xv >> 8 and key < 32 and not np.any(b["lam"])      # H psi plans: no shear, no pure records
                     f = np.zeros(1 << TILE_BITS)
                     for k in range(int(rec["kb"]), int(rec["kb"] + rec["count"])):
                         packed, u = int(T[k]["packed"]), float(T[k]["u"])
@@ -242,7 +252,18 @@ def random_hamiltonian(n, T, seed, weights=None):
     (14, 120, 3, 6, (0.7, 0.1, 0.1, 0.1)),      # low-weight strings: many groups share a small subspace
     (13, 80, 4, 7, (0.55, 0.0, 0.0, 0.45)),     # diagonal only
 ])
-def test_plan_replay_matches_oracle(n, T, c, seed, weights):
+@pytest.mark.parametrize("planner", [2, 1])
+def test_plan_replay_matches_oracle(n, T, c, seed, weights, planner):
+    """planner 2 (default): collision-greedy subspaces, register subspace spanned by member masks (shear + pure records);
+    planner 1: next-unassigned subspaces, reduced-basis coordinates."""
+    xb.capi.lib().b200vqe_debug_set_planner(planner)
+    try:
+        _plan_replay_matches_oracle(n, T, c, seed, weights, planner)
+    finally:
+        xb.capi.lib().b200vqe_debug_set_planner(2)
+
+
+def _plan_replay_matches_oracle(n, T, c, seed, weights, planner):
     xm, zm, cf = random_hamiltonian(n, T, seed, weights)
     rng = np.random.default_rng(seed + 50)
     psi = rng.normal(size=1 << n) + 1j * rng.normal(size=1 << n)
@@ -253,8 +274,14 @@ def test_plan_replay_matches_oracle(n, T, c, seed, weights):
     e = replay(n, c, B, G, Tt, psi)
     eo, _ = co.expect(n, xm, zm, cf, psi)
     assert abs(e - eo.real) < 1e-11 * np.abs(cf).sum()
-    er = replay_records(n, c, B, get_records(n, c, xm, zm, cf), Tt, psi)
+    R = get_records(n, c, xm, zm, cf)
+    er = replay_records(n, c, B, R, Tt, psi)
     assert abs(er - eo.real) < 1e-11 * np.abs(cf).sum()
+    if planner == 1:
+        assert not np.any(B["lam"])
+    elif weights is None and T >= 30 and c <= 5:
+        # unstructured masks: the register subspace is spanned by member masks, so some records need no partner read
+        assert np.sum(R["key"] >= 32) >= len(B)
     # 2048-amplitude tiles (3 register bits) of the double-buffered kernel
     if c <= 8:
         B2, G2, T2 = get_plan(n, c, xm, zm, cf, tb=11)

@@ -355,6 +355,12 @@ int b200vqe_set_option(b200vqe_handle h, const char *key, const char *value) {
         h->opt_tile_bits = c;
         return 0;
     }
+    if (k == "tile-planner") {
+        const int c = atoi(value);
+        if (c != 1 && c != 2) FAIL(B200VQE_EINVAL, "tile-planner must be 1 or 2");
+        h->opt_tile_planner = c;
+        return 0;
+    }
     if (k == "tile-ctas-per-sm") {
         const int c = atoi(value);
         if (c != 2 && c != 3) FAIL(B200VQE_EINVAL, "tile-ctas-per-sm must be 2 or 3");

@@ -100,5 +100,6 @@ struct b200vqe_ctx {
     int opt_tile_ctas = 2;              // resident CTAs per SM of the tile engine (2 or 3)
     int opt_tile_bits = 12;             // tile of the <psi|H|psi> engine: 12 = 4096 amplitudes single-buffered, 11 = 2048 double-buffered
     int opt_shard_exchange = 0;         // tile H psi on a sharded register: 0 all-gather (auto), 1 pairwise pipeline, 2 needed slabs only (one send/recv group)
+    int opt_tile_planner = 2;           // tile planner version (tile_plan.hpp: 2 = collision-greedy subspaces + sheared register subspace, 1 = first version)
     int opt_tile_chunk_bits = 3;        // C: contiguous amplitudes per chunk = 2^C (128 B at C = 3)
 };

@@ -148,7 +148,9 @@ __device__ __forceinline__ void tile_term(const double (&w)[1 << (RB - 1)], unsi
     }
 }
 
-template <int RB, int WHICH, int XR, int BV, bool PT = false>
+// PURE: the record's (sheared) flip mask has no thread part -- the partner of register r is register r ^ XR of the SAME
+// thread, no shared-memory read at all (tile_plan.hpp, TilePlanOpts::shear)
+template <int RB, int WHICH, int XR, int BV, bool PT = false, bool PURE = false>
 __device__ __forceinline__ void tile_rec_half(const double2 (&a)[1 << RB], const double2 *__restrict__ P, unsigned v0, unsigned rep,
                                               const int4 ra, const int4 rb, const double2 *__restrict__ s_terms, double &acc,
                                               double *part = nullptr) {
@@ -158,7 +160,7 @@ __device__ __forceinline__ void tile_rec_half(const double2 (&a)[1 << RB], const
 #pragma unroll
     for (int i = 0; i < NP; ++i) {
         const int r = ((i >> HS) << (HS + 1)) | (BV << HS) | (i & ((1 << HS) - 1));
-        const double2 b = P[(r ^ XR) << 8];
+        const double2 b = PURE ? a[r ^ XR] : P[(r ^ XR) << 8];
         w[i] = WHICH == 0 ? fma(b.x, a[r].x, b.y * a[r].y) : fma(b.x, a[r].y, -(b.y * a[r].x));
     }
     constexpr double WEIGHT = XR ? 2.0 : 1.0;      // each pair once | every amplitude
@@ -182,18 +184,20 @@ template <int RB, int K, bool PT = false>
 __device__ __forceinline__ void tile_runs(const double2 (&a)[1 << RB], const double2 *__restrict__ tile, unsigned v0, unsigned rep,
                                           const int4 *__restrict__ s_recs, const double2 *__restrict__ s_terms, int &gi, int4 &ra,
                                           int4 &rb, double &acc, double *part = nullptr) {
-    if constexpr (K < kTileRecKeys) {
-        constexpr int WHICH = K >> 4;
+    if constexpr (K < 2 * kTileRecKeys) {
+        constexpr int WHICH = (K >> 4) & 1;
         constexpr int XR = ((K & 15) + 1) & 15;
-        if constexpr (XR < (1 << RB)) {
+        constexpr bool PURE = K >= kTileRecKeys;
+        // a pure record with XR = 0 is the diagonal group x = 0: even nY only
+        if constexpr (XR < (1 << RB) && !(PURE && XR == 0 && WHICH == 1)) {
             while (((unsigned)ra.z >> 16) == (unsigned)K) {
                 const int4 ca = ra, cb = rb;
                 ++gi;
                 ra = s_recs[2 * gi];                                   // next record (or the sentinel)
                 rb = s_recs[2 * gi + 1];
                 const double2 *P = tile + ((v0 ^ (unsigned)ca.z) & 0xffu);     // row 0 of the partner thread
-                tile_rec_half<RB, WHICH, XR, 0, PT>(a, P, v0, rep, ca, cb, s_terms, acc, part);
-                if (XR == 0) tile_rec_half<RB, WHICH, XR, 1, PT>(a, P, v0, rep, ca, cb, s_terms, acc, part);
+                tile_rec_half<RB, WHICH, XR, 0, PT, PURE>(a, P, v0, rep, ca, cb, s_terms, acc, part);
+                if (XR == 0) tile_rec_half<RB, WHICH, XR, 1, PT, PURE>(a, P, v0, rep, ca, cb, s_terms, acc, part);
             }
         }
         tile_runs<RB, K + 1, PT>(a, tile, v0, rep, s_recs, s_terms, gi, ra, rb, acc, part);
@@ -243,7 +247,10 @@ k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_byte
     double acc = 0.0;
     int cur_b = -1;
     unsigned Tc = 0, rb0 = 0, rb1 = 0, rb2 = 0, rb3 = 0;
-    const char *psi_lo = reinterpret_cast<const char *>(psi + lo);   // chunk hi of this thread's column: psi_lo + hi * chunk_bytes
+    unsigned lm0 = 0, lm1 = 0, lm2 = 0, lm3 = 0;                     // shear of the batch, as byte offsets inside a chunk
+    const char *psi_b = reinterpret_cast<const char *>(psi);
+    const unsigned lo_b = lo << 4;
+    const char *psi_lo = reinterpret_cast<const char *>(psi + lo);   // line of this thread's column in chunk hi: psi_lo + hi * chunk_bytes
     unsigned pcA = 0;                    // combo of the two rows this thread prefetches for the next tile
     unsigned rep_next = 0;
     bool have_next = false;
@@ -255,13 +262,14 @@ k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_byte
         if (b != cur_b) {                       // uniform over the CTA
             if (PT && cur_b >= 0) flush_terms();
             __syncthreads();
-            if (threadIdx.x < 32)
+            if (threadIdx.x < kTileBatchWords)
                 reinterpret_cast<uint32_t *>(&sb)[threadIdx.x] = reinterpret_cast<const uint32_t *>(&batches[b])[threadIdx.x];
             __syncthreads();
             cur_b = b;
             Tc = 0;
             for (int i = 0; i < 8 - C; ++i) if ((v0 >> (C + i)) & 1u) Tc ^= sb.basis[i];
             rb0 = sb.basis[M - 4]; rb1 = sb.basis[M - 3]; rb2 = sb.basis[M - 2]; rb3 = sb.basis[M - 1];
+            lm0 = sb.lam[0] << 4; lm1 = sb.lam[1] << 4; lm2 = sb.lam[2] << 4; lm3 = sb.lam[3] << 4;
             // the 8 lanes sharing a 128-byte line split its 16 rows between them: this thread takes rows 2(lane & 7), +1
             pcA = Tc ^ ((v0 & 1u) ? rb1 : 0u) ^ ((v0 & 2u) ? rb2 : 0u) ^ ((v0 & 4u) ? rb3 : 0u);
             have_next = false;
@@ -291,7 +299,9 @@ k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_byte
 #pragma unroll
         for (int r = 0; r < 16; ++r) {
             const unsigned hi = base ^ ((r & 1) ? rb0 : 0u) ^ ((r & 2) ? rb1 : 0u) ^ ((r & 4) ? rb2 : 0u) ^ ((r & 8) ? rb3 : 0u);
-            a[r] = __ldcs(reinterpret_cast<const double2 *>(psi_lo + (unsigned long long)hi * chunk_bytes));   // streamed once per batch
+            // register r holds the amplitude with low index bits lo ^ Lambda(r): still one 128-byte line per 8 lanes
+            const unsigned lor = lo_b ^ ((r & 1) ? lm0 : 0u) ^ ((r & 2) ? lm1 : 0u) ^ ((r & 4) ? lm2 : 0u) ^ ((r & 8) ? lm3 : 0u);
+            a[r] = __ldcs(reinterpret_cast<const double2 *>(psi_b + ((unsigned long long)hi * chunk_bytes + lor)));   // streamed once per batch
         }
         __syncthreads();                        // readers of the previous tile are done
 #pragma unroll
@@ -360,8 +370,9 @@ k_tile_expect_db(const double2 *__restrict__ psi, int C, int M, unsigned chunk_b
     const unsigned lo = v0 & ((1u << C) - 1u);
     double acc = 0.0;
     int cur_b = -1;
-    unsigned Tc = 0, rbv[RB];
-    const char *psi_lo = reinterpret_cast<const char *>(psi + lo);   // chunk hi of this thread's column: psi_lo + hi * chunk_bytes
+    unsigned Tc = 0, rbv[RB], lmv[RB];
+    const char *psi_b = reinterpret_cast<const char *>(psi);
+    const unsigned lo_b = lo << 4;
     const unsigned long long total = (unsigned long long)n_batches * tile_count;
     unsigned p = 0;                      // buffer holding the current tile
     bool in_flight = false;              // the current tile was requested during the previous iteration
@@ -372,10 +383,10 @@ k_tile_expect_db(const double2 *__restrict__ psi, int C, int M, unsigned chunk_b
         double2 *dst = buf + which * TILE + v0;
 #pragma unroll
         for (int r = 0; r < REGS; ++r) {
-            unsigned hi = base;
+            unsigned hi = base, lor = lo_b;
 #pragma unroll
-            for (int k = 0; k < RB; ++k) if (r & (1 << k)) hi ^= rbv[k];
-            cp_async16(dst + ((unsigned)r << 8), psi_lo + (unsigned long long)hi * chunk_bytes);
+            for (int k = 0; k < RB; ++k) if (r & (1 << k)) { hi ^= rbv[k]; lor ^= lmv[k]; }
+            cp_async16(dst + ((unsigned)r << 8), psi_b + ((unsigned long long)hi * chunk_bytes + lor));
         }
         cp_async_commit();
     };
@@ -384,14 +395,14 @@ k_tile_expect_db(const double2 *__restrict__ psi, int C, int M, unsigned chunk_b
         const int b = (int)(w / tile_count);
         if (b != cur_b) {                       // uniform over the CTA; no request is in flight across a batch switch
             __syncthreads();
-            if (threadIdx.x < 32)
+            if (threadIdx.x < kTileBatchWords)
                 reinterpret_cast<uint32_t *>(&sb)[threadIdx.x] = reinterpret_cast<const uint32_t *>(&batches[b])[threadIdx.x];
             __syncthreads();
             cur_b = b;
             Tc = 0;
             for (int i = 0; i < 8 - C; ++i) if ((v0 >> (C + i)) & 1u) Tc ^= sb.basis[i];
 #pragma unroll
-            for (int k = 0; k < RB; ++k) rbv[k] = sb.basis[M - RB + k];
+            for (int k = 0; k < RB; ++k) { rbv[k] = sb.basis[M - RB + k]; lmv[k] = sb.lam[k] << 4; }
             const int n_r = sb.r_end - sb.r_begin;
             const int n_t = sb.t_end - sb.t_begin;
             const int4 *rsrc = reinterpret_cast<const int4 *>(recs + sb.r_begin);
@@ -530,7 +541,7 @@ k_tile_apply(const double2 *__restrict__ src, double2 *__restrict__ dst, int C, 
     __shared__ __align__(16) double2 s_terms[kStageTerms];
     const unsigned v0 = threadIdx.x;
     const unsigned lo = v0 & ((1u << C) - 1u);
-    if (threadIdx.x < 32) reinterpret_cast<uint32_t *>(&sb)[threadIdx.x] = reinterpret_cast<const uint32_t *>(batch)[threadIdx.x];
+    if (threadIdx.x < kTileBatchWords) reinterpret_cast<uint32_t *>(&sb)[threadIdx.x] = reinterpret_cast<const uint32_t *>(batch)[threadIdx.x];
     __syncthreads();
     unsigned Tc = 0;
     for (int i = 0; i < 8 - C; ++i) if ((v0 >> (C + i)) & 1u) Tc ^= sb.basis[i];

@@ -22,6 +22,7 @@
 // batch's records and terms always fit the kernels' shared-memory staging.
 #pragma once
 #include <algorithm>
+#include <cmath>
 #include <cstdint>
 #include <unordered_map>
 #include <vector>
@@ -36,15 +37,19 @@ constexpr int kTileMaxDim = 10;      // M = kTileBits - C, C >= 2
 
 constexpr int kTileClasses = 5;      // groups of a batch are ordered by hsel = 0, 1, 2, 3, -1
 
-struct TileBatch {                   // 128 bytes
+struct TileBatch {                   // 160 bytes
     uint32_t basis[kTileMaxDim];     // basis[i] <-> virtual bit C + i; acts on the high index (j >> C), n - C <= 32
     uint32_t seg[kTileMaxDim + 1];   // coset representative of tile t:  rep = OR_i (t & seg[i]) << i  (zeros at the pivots)
     int32_t g_begin, g_end;          // groups of this batch
     int32_t t_begin, t_end;          // terms of this batch
     int32_t cls_end[kTileClasses];   // end of each hsel class, relative to g_begin
     int32_t r_begin, r_end;          // TileRec range of this batch (expectation engine; see build_tile_records)
+    uint32_t lam[4];                 // shear: register r of a thread holds the amplitude with low index bits lo ^ Lambda(r),
+                                     // Lambda(r) = XOR of lam[k] over the set bits k of r (0 for plans built without shear)
+    uint32_t pad[4];
 };
-static_assert(sizeof(TileBatch) == 128, "TileBatch layout");
+constexpr int kTileBatchWords = 40;
+static_assert(sizeof(TileBatch) == 4 * kTileBatchWords, "TileBatch layout");
 
 struct TileGroup {                   // 16 bytes
     uint32_t kb;                     // first term
@@ -77,7 +82,7 @@ struct TileRec {                     // 32 bytes
 };
 static_assert(sizeof(TileRec) == 32, "TileRec layout");
 
-constexpr int kTileRecKeys = 32;
+constexpr int kTileRecKeys = 32;      // (which, XR) combinations; + 32: pure-register records (expectation engine)
 constexpr int kStageRecs = 128;      // records / terms of one batch staged in shared memory by k_tile_expect;
 constexpr int kStageTerms = 256;     // expectation plans are built with these as per-batch capacities
 constexpr int kStageGroupsCap = kStageRecs / 2;
@@ -138,19 +143,86 @@ inline uint16_t sign_word16(unsigned zr) {   // bit r = parity(r & zr), r = 0..1
 
 }  // namespace tileplan
 
+// How a plan is built.
+//   pair_weights: expectation plans double the coefficients of groups evaluated once per pair; apply plans do not.
+//   natural (n == tile_bits only): one batch whose virtual index equals the amplitude index (basis = unit vectors in
+//     order), for kernels that keep the whole register in shared memory in its natural order (k_sweep_small).
+//   max_groups / max_terms (0 = unlimited): capacity of one batch; an xmask group with more terms than max_terms is cut
+//     into several groups of the same x.
+//   collide: choose every new basis vector of a batch's subspace as the coset (modulo the vectors chosen so far) that
+//     holds the most unassigned groups, instead of the next unassigned group: random masks then give ~12 instead of
+//     ~9 groups per 9-dimensional batch, structured ones collapse as before.
+//   shear: choose the virtual coordinate system so that the register subspace (the RB virtual bits a thread keeps in its
+//     own registers) is spanned by the full virtual masks of RB member groups -- their partner amplitude then sits in
+//     the SAME thread (no shared-memory read: "pure" records) -- which needs the low-index shear TileBatch::lam, and
+//     tilt the remaining coordinates so that the other groups have a register component (8 instead of 16 partner reads).
+struct TilePlanOpts {
+    bool pair_weights = true;
+    bool natural = false;
+    size_t max_groups = 0, max_terms = 0;
+    int tile_bits = kTileBits;
+    bool collide = false;
+    bool shear = false;
+};
+
+namespace tileplan {
+
+// rows of the inverse of the M x M matrix over GF(2) whose COLUMN i is col[i]:  coordinate i of c = parity(inv[i] & c)
+inline std::vector<uint64_t> invert_columns(const std::vector<uint64_t> &col, int M) {
+    std::vector<uint64_t> row(M, 0), inv(M, 0);
+    for (int r = 0; r < M; ++r) {
+        for (int i = 0; i < M; ++i) row[r] |= ((col[i] >> r) & 1ull) << i;
+        inv[r] = 1ull << r;
+    }
+    for (int c = 0; c < M; ++c) {
+        int p = -1;
+        for (int r = c; r < M; ++r) if ((row[r] >> c) & 1) { p = r; break; }
+        if (p < 0) return {};                      // singular: the caller passes a basis
+        std::swap(row[c], row[p]);
+        std::swap(inv[c], inv[p]);
+        for (int r = 0; r < M; ++r)
+            if (r != c && ((row[r] >> c) & 1)) { row[r] ^= row[c]; inv[r] ^= inv[c]; }
+    }
+    return inv;
+}
+
+// counts equal keys of one pass over at most 65536 positions (open addressing, stamped instead of cleared)
+struct KeyCounter {
+    struct Slot { uint64_t key; uint32_t stamp; uint16_t cnt; uint16_t first; };
+    std::vector<Slot> t;
+    uint32_t now = 0;
+    size_t mask = 0;
+    void reserve(size_t n) {
+        size_t cap = 16;
+        while (cap < 2 * n) cap <<= 1;
+        if (cap > t.size()) { t.assign(cap, Slot{0, 0, 0, 0}); now = 0; }
+        mask = t.size() - 1;
+    }
+    void begin() { ++now; }
+    // counts `key`; returns its slot (first = position of its first occurrence)
+    const Slot &add(uint64_t key, uint32_t pos) {
+        size_t h = (size_t)((key * 0x9E3779B97F4A7C15ull) >> 24) & mask;
+        for (;;) {
+            Slot &s = t[h];
+            if (s.stamp != now) { s.stamp = now; s.key = key; s.cnt = 1; s.first = (uint16_t)pos; return s; }
+            if (s.key == key) { ++s.cnt; return s; }
+            h = (h + 1) & mask;
+        }
+    }
+};
+
+}  // namespace tileplan
+
 // terms: non-identity terms with u already set (coef or i*coef, real part).  Groups of equal x.
-// pair_weights: expectation plans double the coefficients of groups evaluated once per pair; apply plans do not.
-// natural (n == kTileBits only): one batch whose virtual index equals the amplitude index (basis = unit vectors in order),
-// for kernels that keep the whole register in shared memory in its natural order (k_sweep_small).
-// max_groups / max_terms (0 = unlimited): capacity of one batch; an xmask group with more terms than max_terms is cut
-// into several groups of the same x.
-inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> &in, bool pair_weights = true, bool natural = false,
-                                size_t max_groups = 0, size_t max_terms = 0, int tile_bits = kTileBits) {
+inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> &in, const TilePlanOpts &o) {
     using namespace tileplan;
-    const int TB = tile_bits, RB = tile_bits - kTileThreadBits;      // tile bits, register bits (4 or 3)
+    const int TB = o.tile_bits, RB = o.tile_bits - kTileThreadBits;      // tile bits, register bits (4 or 3)
+    const bool natural = o.natural;
+    const size_t max_groups = o.max_groups, max_terms = o.max_terms;
     TilePlan P;
     P.n = n; P.C = C; P.M = TB - C; P.TB = TB;
     const int M = P.M;
+    const int TD = M - RB;                        // thread coordinates (virtual bits C .. C+TD-1); may be 0
     const int nh = n - C;                         // bits of the high index
     const uint64_t lomask = (1ull << C) - 1;
 
@@ -162,40 +234,89 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
         if (in[a].odd != in[b].odd) return in[a].odd < in[b].odd;
         return in[a].z < in[b].z;
     });
-    struct G { uint64_t x; size_t tb, te; };
+    struct G { uint64_t x; size_t tb, te; int recs; };
     std::vector<G> gs;
     for (size_t i = 0; i < order.size();) {
         size_t j = i;
         while (j < order.size() && in[order[j]].x == in[order[i]].x && (!max_terms || j - i < max_terms)) ++j;
-        gs.push_back(G{in[order[i]].x, i, j});
+        const int recs = (in[order[i]].odd != in[order[j - 1]].odd) ? 2 : 1;     // even-nY and odd-nY terms are separate records
+        gs.push_back(G{in[order[i]].x, i, j, recs});
         i = j;
     }
     const size_t NG = gs.size();
-    std::unordered_map<uint64_t, std::vector<size_t>> by_hi;
+    std::unordered_map<uint64_t, std::vector<uint32_t>> by_hi;
     by_hi.reserve(NG * 2);
-    for (size_t g = 0; g < NG; ++g) by_hi[gs[g].x >> C].push_back(g);
+    for (size_t g = 0; g < NG; ++g) by_hi[gs[g].x >> C].push_back((uint32_t)g);
     std::vector<char> done(NG, 0);
     size_t n_done = 0, cursor = 0;
+    // the subspace of a batch is chosen among the next kWindow unassigned groups (bounds the cost per batch); its members
+    // are then collected from ALL unassigned groups
+    constexpr size_t kWindow = 4096;
+    std::vector<uint32_t> win;
+    std::vector<uint64_t> wkey;                   // high mask of a window group reduced modulo the subspace under construction
+    KeyCounter kc;
+    kc.reserve(kWindow);
 
     while (n_done < NG) {
         while (done[cursor]) ++cursor;
-        // ---- choose the subspace: greedy over the next unassigned groups ----
+        win.clear();
+        wkey.clear();
+        for (size_t g = cursor; g < NG && win.size() < kWindow; ++g)
+            if (!done[g]) { win.push_back((uint32_t)g); wkey.push_back(gs[g].x >> C); }
+        // ---- choose the subspace ----
         Rref rr;
-        size_t scanned = 0;
+        auto add = [&](uint64_t v) {              // v: reduced, non-zero
+            const int p = 63 - __builtin_clzll(v);
+            rr.insert(v);
+            uint64_t *k = wkey.data();
+            const size_t nw = wkey.size();
+            for (size_t i = 0; i < nw; ++i) k[i] ^= v & (0ull - ((k[i] >> p) & 1ull));
+        };
         if (natural) {
             // unit vectors inserted from the top bit down stay unit vectors: basis index i <-> high bit nh-1-i
-            for (int p = nh - 1; p >= 0; --p) rr.insert(1ull << p);
+            for (int p = nh - 1; p >= 0; --p) add(1ull << p);
         }
-        for (size_t g = cursor; g < NG && (int)rr.b.size() < M && scanned < 8192; ++g) {
-            if (done[g]) continue;
-            ++scanned;
-            rr.insert(gs[g].x >> C);
+        size_t scan = 0;
+        while ((int)rr.b.size() < M) {
+            uint64_t pick = 0;
+            const int d = (int)rr.b.size();
+            // expected number of window pairs that agree modulo the current span; below ~1/2 a counting pass finds nothing
+            const double pairs = 0.5 * (double)win.size() * (double)win.size() * std::ldexp(1.0, d - nh);
+            uint64_t pick2 = 0;                   // runner-up of a counting pass, when it holds a collision too
+            if (o.collide && d >= 1 && pairs >= 0.5) {
+                // the coset holding the most window groups (ties: the one met first)
+                kc.begin();
+                uint32_t best = 0, best_first = 0, second = 0;
+                for (size_t i = 0; i < wkey.size(); ++i) {
+                    const uint64_t k = wkey[i];
+                    if (!k) continue;
+                    const KeyCounter::Slot &sl = kc.add(k, (uint32_t)i);
+                    if (k == pick) best = sl.cnt;
+                    else if (sl.cnt > best || (sl.cnt == best && sl.first < best_first)) {
+                        second = best; pick2 = pick;
+                        best = sl.cnt; best_first = sl.first; pick = k;
+                    } else if (k == pick2) second = sl.cnt;
+                    else if (sl.cnt > second) { second = sl.cnt; pick2 = k; }
+                }
+                if (second < 2) pick2 = 0;
+            } else {
+                while (scan < wkey.size() && !wkey[scan]) ++scan;
+                if (scan < wkey.size()) pick = wkey[scan];
+            }
+            if (!pick) break;                     // every window group already lies in the span
+            add(pick);
+            if (pick2 && (int)rr.b.size() < M) {
+                const uint64_t v = rr.reduce(pick2);
+                if (v) add(v);
+            }
         }
-        for (int p = 0; p < nh && (int)rr.b.size() < M; ++p) rr.insert(1ull << p);   // pad with unit vectors
-        // ---- members: every unassigned group whose high mask lies in the span ----
+        for (int p = 0; p < nh && (int)rr.b.size() < M; ++p) {   // pad with unit vectors
+            const uint64_t v = rr.reduce(1ull << p);
+            if (v) add(v);
+        }
+        // ---- members: every unassigned group whose high mask lies in the span, in ascending order ----
         std::vector<size_t> members;
-        const size_t remaining = NG - n_done;
-        if (remaining <= (1ull << rr.b.size())) {
+        if (NG - n_done <= (1ull << rr.b.size())) {
             for (size_t g = cursor; g < NG; ++g)
                 if (!done[g] && rr.reduce(gs[g].x >> C) == 0) members.push_back(g);
         } else {
@@ -204,7 +325,7 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
                 for (size_t i = 0; i < rr.b.size(); ++i) if ((m >> i) & 1) v ^= rr.b[i];
                 auto it = by_hi.find(v);
                 if (it == by_hi.end()) continue;
-                for (size_t g : it->second) if (!done[g]) members.push_back(g);
+                for (uint32_t g : it->second) if (!done[g]) members.push_back(g);
             }
             std::sort(members.begin(), members.end());
         }
@@ -217,75 +338,154 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
             }
             members.resize(keep);
         }
-        // ---- order the basis: the RB coordinates that cover most work go on the register bits ----
-        const int dim = (int)rr.b.size();
-        std::vector<uint64_t> mu(members.size());
-        std::vector<double> cost(members.size());
-        for (size_t k = 0; k < members.size(); ++k) {
-            mu[k] = rr.coords(gs[members[k]].x >> C);
-            cost[k] = 4.0 + (double)(gs[members[k]].te - gs[members[k]].tb);
-        }
-        std::vector<int> perm;                     // perm[new position] = old index
-        std::vector<char> used(dim, 0), covered(members.size(), 0);
-        std::vector<int> top;
-        for (int pick = 0; pick < RB && pick < dim; ++pick) {
-            int best = -1;
-            double bestw = -1.0;
-            for (int i = 0; i < dim; ++i) {
-                if (used[i]) continue;
-                double w = 0.0;
-                for (size_t k = 0; k < members.size(); ++k) if (!covered[k] && ((mu[k] >> i) & 1)) w += cost[k];
-                if (w > bestw) { bestw = w; best = i; }
-            }
-            used[best] = 1;
-            top.push_back(best);
-            for (size_t k = 0; k < members.size(); ++k) if ((mu[k] >> best) & 1) covered[k] = 1;
-        }
+        for (size_t g : members) { done[g] = 1; ++n_done; }
+        const int dim = (int)rr.b.size();          // == M (n >= tile_bits)
+        const size_t NM = members.size();
+        std::vector<uint64_t> cc(NM);              // coordinates in the reduced basis rr.b
+        std::vector<uint32_t> lo(NM);
+        for (size_t k = 0; k < NM; ++k) { cc[k] = rr.coords(gs[members[k]].x >> C); lo[k] = (uint32_t)(gs[members[k]].x & lomask); }
+
+        // ---- virtual coordinates: newb[i] (in rr coordinates) <-> virtual bit C + i; the top RB are the register bits ----
+        std::vector<uint64_t> newb;
+        uint32_t lam[4] = {0, 0, 0, 0};
         if (natural) {
-            perm.clear();
-            for (int i = 0; i < dim; ++i) perm.push_back(dim - 1 - i);     // virtual bit C+i <-> high bit i
+            for (int i = 0; i < dim; ++i) newb.push_back(1ull << (dim - 1 - i));      // virtual bit C+i <-> high bit i
+        } else if (!o.shear) {
+            // the RB reduced-basis coordinates that cover most work go on the register bits
+            std::vector<double> cost(NM);
+            for (size_t k = 0; k < NM; ++k) cost[k] = 4.0 + (double)(gs[members[k]].te - gs[members[k]].tb);
+            std::vector<char> used(dim, 0), covered(NM, 0);
+            std::vector<int> top;
+            for (int pick = 0; pick < RB && pick < dim; ++pick) {
+                int best = -1;
+                double bestw = -1.0;
+                for (int i = 0; i < dim; ++i) {
+                    if (used[i]) continue;
+                    double w = 0.0;
+                    for (size_t k = 0; k < NM; ++k) if (!covered[k] && ((cc[k] >> i) & 1)) w += cost[k];
+                    if (w > bestw) { bestw = w; best = i; }
+                }
+                used[best] = 1;
+                top.push_back(best);
+                for (size_t k = 0; k < NM; ++k) if ((cc[k] >> best) & 1) covered[k] = 1;
+            }
+            for (int i = 0; i < dim; ++i) if (!used[i]) newb.push_back(1ull << i);
+            for (int t : top) newb.push_back(1ull << t);
         } else {
-            for (int i = 0; i < dim; ++i) if (!used[i]) perm.push_back(i);
-            for (int t : top) perm.push_back(t);       // register bits are the top RB coordinates
+            // register subspace R = span of the full virtual masks V = (cc << C | lo) of RB members with independent cc,
+            // chosen greedily for the number of member records inside the span (those become pure-register records)
+            std::vector<uint64_t> V(NM);
+            for (size_t k = 0; k < NM; ++k) V[k] = (cc[k] << C) | lo[k];
+            Rref rc, rv;
+            std::vector<uint64_t> rho;
+            for (int pick = 0; pick < RB; ++pick) {
+                int best = -1, best_score = -1;
+                for (size_t k = 0; k < NM; ++k) {
+                    if (!cc[k] || !rc.reduce(cc[k])) continue;
+                    Rref t = rv;
+                    t.insert(V[k]);
+                    int score = 0;
+                    for (size_t m = 0; m < NM; ++m) if (cc[m] && !t.reduce(V[m])) score += gs[members[m]].recs;
+                    if (score > best_score) { best_score = score; best = (int)k; }
+                }
+                if (best < 0) break;
+                rv.insert(V[best]);
+                rc.insert(cc[best]);
+                lam[rho.size()] = lo[best];
+                rho.push_back(cc[best]);
+            }
+            for (int i = 0; i < dim && (int)rho.size() < RB; ++i)
+                if (rc.reduce(1ull << i)) { rc.insert(1ull << i); rho.push_back(1ull << i); }
+            std::vector<uint64_t> theta;
+            for (int i = 0; i < dim && (int)theta.size() < TD; ++i)
+                if (rc.reduce(1ull << i)) { rc.insert(1ull << i); theta.push_back(1ull << i); }
+            newb = theta;
+            newb.insert(newb.end(), rho.begin(), rho.end());
+            // tilt: theta_j += sum_k s_jk rho_k changes the register part of a member with thread part t to a ^ XOR_{j in t} s_j
+            const std::vector<uint64_t> inv = invert_columns(newb, dim);
+            std::vector<uint32_t> tt(NM), aa(NM);
+            for (size_t k = 0; k < NM; ++k) {
+                uint64_t m = 0;
+                for (int i = 0; i < dim; ++i) m |= (uint64_t)parity64h(inv[i] & cc[k]) << i;
+                tt[k] = (uint32_t)(m & ((1ull << TD) - 1));
+                aa[k] = (uint32_t)(m >> TD);
+            }
+            std::vector<uint32_t> s(TD, 0);
+            auto total_cost = [&]() {
+                int c = 0;
+                for (size_t k = 0; k < NM; ++k) {
+                    if (!tt[k]) continue;         // pure or register-only: not affected by the tilt
+                    uint32_t a = aa[k];
+                    for (int j = 0; j < TD; ++j) if ((tt[k] >> j) & 1) a ^= s[j];
+                    c += (a ? 1 : 2) * gs[members[k]].recs;
+                }
+                return c;
+            };
+            for (int round = 0; round < 2; ++round)
+                for (int j = 0; j < TD; ++j) {
+                    int best_c = -1;
+                    uint32_t best_s = 0;
+                    for (uint32_t cand = 0; cand < (1u << RB); ++cand) {
+                        s[j] = cand;
+                        const int c = total_cost();
+                        if (best_c < 0 || c < best_c) { best_c = c; best_s = cand; }
+                    }
+                    s[j] = best_s;
+                }
+            for (int j = 0; j < TD; ++j)
+                for (int k = 0; k < RB; ++k) if ((s[j] >> k) & 1) newb[j] ^= rho[k];
         }
 
         TileBatch B{};
-        for (int i = 0; i < dim; ++i) B.basis[i] = (uint32_t)rr.b[perm[i]];
+        for (int i = 0; i < dim; ++i) {
+            uint64_t v = 0;
+            for (int q = 0; q < dim; ++q) if ((newb[i] >> q) & 1) v ^= rr.b[q];
+            B.basis[i] = (uint32_t)v;
+        }
+        for (int k = 0; k < 4; ++k) B.lam[k] = lam[k];
+        auto shear_of = [&](unsigned reg) {        // Lambda(reg)
+            uint32_t l = 0;
+            for (int k = 0; k < RB; ++k) if ((reg >> k) & 1) l ^= lam[k];
+            return l;
+        };
+        const std::vector<uint64_t> inv = invert_columns(newb, dim);
         std::vector<int> sp(rr.piv.begin(), rr.piv.end());
         std::sort(sp.begin(), sp.end());
         {   // tile index bits [lo_i, hi_i) move up by i = number of pivots below them
-            int lo = 0;
+            int lob = 0;
             for (int i = 0; i <= dim; ++i) {
-                const int hi = i < dim ? sp[i] - i : 32;
+                const int hib = i < dim ? sp[i] - i : 32;
                 uint64_t m = 0;
-                if (hi > lo) m = ((hi >= 32 ? (1ull << 32) : (1ull << hi)) - 1) & ~((1ull << lo) - 1);
+                if (hib > lob) m = ((hib >= 32 ? (1ull << 32) : (1ull << hib)) - 1) & ~((1ull << lob) - 1);
                 B.seg[i] = (uint32_t)m;
-                lo = hi;
+                lob = hib;
             }
         }
         B.g_begin = (int32_t)P.groups.size();
         B.t_begin = (int32_t)P.terms.size();
-        auto permute_mu = [&](uint64_t m) {
-            uint64_t r = 0;
-            for (int i = 0; i < dim; ++i) r |= ((m >> perm[i]) & 1ull) << i;
-            return r;
-        };
+        // sheared virtual flip mask of every member
+        std::vector<uint16_t> xvs(NM);
+        for (size_t k = 0; k < NM; ++k) {
+            uint64_t m = 0;
+            for (int i = 0; i < dim; ++i) m |= (uint64_t)parity64h(inv[i] & cc[k]) << i;
+            const unsigned xv = (unsigned)((m << C) | lo[k]);
+            xvs[k] = (uint16_t)(xv ^ shear_of(xv >> (TB - RB)));
+        }
         // order the members by pair-selector class (hsel 0, 1, 2, 3, then -1): one code path per class on the device
         auto class_of = [&](size_t k) {
-            const unsigned xr = (unsigned)(((permute_mu(mu[k]) << C) >> (TB - RB)) & ((1u << RB) - 1));
+            const unsigned xr = (unsigned)xvs[k] >> (TB - RB);
             return xr ? 31 - __builtin_clz(xr) : kTileClasses - 1;
         };
-        std::vector<size_t> ord(members.size());
-        for (size_t k = 0; k < ord.size(); ++k) ord[k] = k;
+        std::vector<size_t> ord(NM);
+        for (size_t k = 0; k < NM; ++k) ord[k] = k;
         std::stable_sort(ord.begin(), ord.end(), [&](size_t a, size_t b) { return class_of(a) < class_of(b); });
         for (int c = 0; c < kTileClasses; ++c) B.cls_end[c] = 0;
-        for (size_t kk = 0; kk < members.size(); ++kk) {
+        for (size_t kk = 0; kk < NM; ++kk) {
             const size_t k = ord[kk];
             for (int c = class_of(k); c < kTileClasses; ++c) ++B.cls_end[c];
             const G &g = gs[members[k]];
-            const uint64_t m = permute_mu(mu[k]);
             TileGroup tg{};
-            tg.xv = (uint16_t)((m << C) | (g.x & lomask));
+            tg.xv = xvs[k];
             const unsigned xr = tg.xv >> (TB - RB);
             tg.hsel = xr ? (int16_t)(31 - __builtin_clz(xr)) : (int16_t)-1;
             const double weight = tg.hsel >= 0 ? 2.0 : 1.0;
@@ -293,21 +493,22 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
             for (size_t t = g.tb; t < g.te; ++t) {
                 const TilePlanTermIn &ti = in[order[t]];
                 const uint64_t zhi = ti.z >> C;
+                const uint32_t zlo = (uint32_t)(ti.z & lomask);
                 uint64_t Zv = 0;
                 for (int i = 0; i < dim; ++i) Zv |= (uint64_t)parity64h((uint64_t)B.basis[i] & zhi) << i;
-                const unsigned zv = (unsigned)((Zv << C) | (ti.z & lomask));
+                unsigned zv = (unsigned)((Zv << C) | zlo);
+                // parity(v_phys & zv) with v_phys = v ^ Lambda(reg(v)):  register bit k of z picks up parity(lam[k] & z_lo)
+                for (int k2 = 0; k2 < RB; ++k2) zv ^= (unsigned)parity64h((uint64_t)(lam[k2] & zlo)) << (TB - RB + k2);
                 TileTerm tt;
                 tt.packed = (zhi & 0xffffffffull) | ((uint64_t)(zv & 0xffu) << 32) |
                             ((uint64_t)((zv >> (TB - RB)) & 0xfu) << 40) |
                             ((uint64_t)sign_word16((zv >> (TB - RB)) & 0xfu) << 48);
-                tt.u = (pair_weights ? weight : 1.0) * ti.u;
+                tt.u = (o.pair_weights ? weight : 1.0) * ti.u;
                 P.terms.push_back(tt);
                 P.term_src.push_back(ti.idx);
                 ti.odd ? ++tg.n_odd : ++tg.n_even;
             }
             P.groups.push_back(tg);
-            done[members[k]] = 1;
-            ++n_done;
         }
         B.g_end = (int32_t)P.groups.size();
         B.t_end = (int32_t)P.terms.size();
@@ -316,14 +517,40 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
     return P;
 }
 
-// Records of the expectation kernel for a plan built with pair_weights = true and the kStage* capacities.
-inline void build_tile_records(TilePlan &P) {
+// the signature of the first version: reduced-basis coordinates, next-unassigned subspace choice
+inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> &in, bool pair_weights = true, bool natural = false,
+                                size_t max_groups = 0, size_t max_terms = 0, int tile_bits = kTileBits) {
+    TilePlanOpts o;
+    o.pair_weights = pair_weights; o.natural = natural; o.max_groups = max_groups; o.max_terms = max_terms; o.tile_bits = tile_bits;
+    return build_tile_plan(n, C, in, o);
+}
+
+// The plans the backend builds (planner: 2 = collision-greedy subspaces + sheared register subspace [default],
+// 1 = the first version: next-unassigned subspaces, reduced-basis coordinates).
+inline TilePlanOpts expect_plan_opts(int tile_bits, int planner = 2) {
+    TilePlanOpts o;
+    o.pair_weights = true; o.max_groups = kStageGroupsCap; o.max_terms = kStageTerms; o.tile_bits = tile_bits;
+    o.collide = planner >= 2; o.shear = planner >= 2;
+    return o;
+}
+inline TilePlanOpts apply_plan_opts(int planner = 2) {
+    TilePlanOpts o;
+    o.pair_weights = false; o.max_groups = kStageGroupsCap; o.max_terms = kStageTerms; o.tile_bits = kTileBits;
+    o.collide = planner >= 2; o.shear = false;       // H psi reads all 16 partner rows whatever the coordinates
+    return o;
+}
+
+// Records of the tile kernels for a plan built with the kStage* capacities.  allow_pure (expectation plans built with
+// shear): a record whose sheared flip mask has no thread part gets key + 32 -- the kernel then takes the partner from
+// the thread's own registers.
+inline void build_tile_records(TilePlan &P, bool allow_pure = false) {
     P.recs.clear();
     for (TileBatch &B : P.batches) {
         std::vector<TileRec> rs;
         for (int g = B.g_begin; g < B.g_end; ++g) {
             const TileGroup &tg = P.groups[g];
             const unsigned xr = tg.xv >> kTileThreadBits;
+            const bool pure = allow_pure && (tg.xv & ((1u << kTileThreadBits) - 1)) == 0;
             for (int which = 0; which < 2; ++which) {
                 const uint32_t cnt = which ? tg.n_odd : tg.n_even;
                 if (!cnt) continue;
@@ -331,7 +558,7 @@ inline void build_tile_records(TilePlan &P) {
                 r.kb = tg.kb + (which ? tg.n_even : 0);
                 r.count = cnt;
                 r.xv = tg.xv;
-                r.key = (uint8_t)(which * 16 + (xr ? xr - 1 : 15));
+                r.key = (uint8_t)((pure ? 32 : 0) + which * 16 + (xr ? xr - 1 : 15));
                 r.packed0 = P.terms[r.kb].packed;
                 r.u0 = P.terms[r.kb].u;
                 rs.push_back(r);
