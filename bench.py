@@ -208,6 +208,8 @@ def run_gpu(args):
     be.set_option("tile-bits", args.tile_bits)
     be.set_option("tile-ctas-per-sm", args.tile_ctas)
     be.set_option("tile-planner", args.planner)
+    be.set_option("tile-dispatch", args.dispatch)
+    be.set_option("expect-kernel", args.expect_kernel)
     be.set_hamiltonian(xm, zm, cf)
     Tn, G = be.hamiltonian_stats()
 
@@ -404,6 +406,8 @@ def main():
     ap.add_argument("--engine", default="auto", choices=["auto", "tile", "stream"], help="<psi|H|psi> kernel family")
     ap.add_argument("--tile-ctas", type=int, default=2, choices=[2, 3], help="tile engine: resident CTAs per SM")
     ap.add_argument("--tile-bits", type=int, default=12, choices=[11, 12], help="tile engine: 12 = 4096-amplitude tiles, 11 = 2048 double-buffered")
+    ap.add_argument("--expect-kernel", default="auto", choices=["auto", "pipe", "ring", "classic"])
+    ap.add_argument("--dispatch", type=int, default=1, choices=[0, 1, 2, 3])
     ap.add_argument("--planner", type=int, default=2, choices=[1, 2], help="tile planner version (csrc/tile_plan.hpp)")
     ap.add_argument("--chunk-bits", type=int, default=3, help="tile engine: log2 contiguous amplitudes per HBM chunk")
     args = ap.parse_args()

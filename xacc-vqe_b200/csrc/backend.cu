@@ -4,6 +4,7 @@
 #include "kernels_apply.cuh"
 #include "kernels_small.cuh"
 #include "kernels_tile.cuh"
+#include "kernels_tile_ring.cuh"
 #include "pauli_host.hpp"
 
 #include <algorithm>
@@ -234,10 +235,15 @@ static int create_common(int n_qubits, int device, int rank, int world, const ch
         cudaError_t ea = cudaSuccess;
         auto set = [&](const void *f, int bytes) { if (ea == cudaSuccess) ea = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes); };
         set((const void *)k_tile_expect<2, false>, tile);
-        set((const void *)k_tile_expect<3, false>, tile);
-        set((const void *)k_tile_expect<2, true>, tile);
+        set((const void *)k_tile_expect<2, false, 1>, tile);
+        set((const void *)k_tile_expect<2, false, 2>, tile);
+        set((const void *)k_tile_expect<2, false, 3>, tile);
+        set((const void *)k_tile_expect<3, false, 1>, tile);
+        set((const void *)k_tile_expect<2, true, 1>, tile);
         set((const void *)k_tile_expect_db<3>, two_small);
         set((const void *)k_tile_apply, tile);
+        set((const void *)k_tile_expect_ring, kRingSmemBytes);
+        set((const void *)k_tile_expect_pipe, kPipeSmemBytes);
         set((const void *)k_sweep_small, tile);
         if (ea != cudaSuccess) return fail(std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(ea), B200VQE_ECUDA);
     }
@@ -353,6 +359,19 @@ int b200vqe_set_option(b200vqe_handle h, const char *key, const char *value) {
         const int c = atoi(value);
         if (c != kTileBitsSmall && c != kTileBits) FAIL(B200VQE_EINVAL, "tile-bits must be 11 or 12");
         h->opt_tile_bits = c;
+        return 0;
+    }
+    if (k == "expect-kernel") {
+        if (v == "auto" || v == "pipe") h->opt_expect_kernel = 0;
+        else if (v == "classic") h->opt_expect_kernel = 1;
+        else if (v == "ring") h->opt_expect_kernel = 2;
+        else FAIL(B200VQE_EINVAL, "expect-kernel must be auto, pipe, ring or classic");
+        return 0;
+    }
+    if (k == "tile-dispatch") {
+        const int c = atoi(value);
+        if (c < 0 || c > 3) FAIL(B200VQE_EINVAL, "tile-dispatch must be 0..3");
+        h->opt_tile_dispatch = c;
         return 0;
     }
     if (k == "tile-planner") {

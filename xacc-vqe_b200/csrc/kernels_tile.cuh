@@ -180,11 +180,12 @@ __device__ __forceinline__ void tile_rec_half(const double2 (&a)[1 << RB], const
 }
 
 // all records of the batch, key by key: s_recs holds (n_r + 1) records as int4 pairs, the last one a sentinel (key 255)
-template <int RB, int K, bool PT = false>
+// NK = number of keys compiled in: 2 * kTileRecKeys (generic + pure-register records) or kTileRecKeys (generic only)
+template <int RB, int K, bool PT = false, int NK = 2 * kTileRecKeys>
 __device__ __forceinline__ void tile_runs(const double2 (&a)[1 << RB], const double2 *__restrict__ tile, unsigned v0, unsigned rep,
                                           const int4 *__restrict__ s_recs, const double2 *__restrict__ s_terms, int &gi, int4 &ra,
                                           int4 &rb, double &acc, double *part = nullptr) {
-    if constexpr (K < 2 * kTileRecKeys) {
+    if constexpr (K < NK) {
         constexpr int WHICH = (K >> 4) & 1;
         constexpr int XR = ((K & 15) + 1) & 15;
         constexpr bool PURE = K >= kTileRecKeys;
@@ -200,7 +201,73 @@ __device__ __forceinline__ void tile_runs(const double2 (&a)[1 << RB], const dou
                 if (XR == 0) tile_rec_half<RB, WHICH, XR, 1, PT, PURE>(a, P, v0, rep, ca, cb, s_terms, acc, part);
             }
         }
-        tile_runs<RB, K + 1, PT>(a, tile, v0, rep, s_recs, s_terms, gi, ra, rb, acc, part);
+        tile_runs<RB, K + 1, PT, NK>(a, tile, v0, rep, s_recs, s_terms, gi, ra, rb, acc, part);
+    }
+}
+
+// the same walk with one jump-table dispatch per record instead of the chain of key tests (whose branch sites are spread over
+// the whole function: 64 instruction-cache lines per tile)
+template <int RB, int K, bool PT>
+__device__ __forceinline__ void tile_one(const double2 (&a)[1 << RB], const double2 *__restrict__ tile, unsigned v0, unsigned rep,
+                                         const int4 ca, const int4 cb, const double2 *__restrict__ s_terms, double &acc, double *part) {
+    constexpr int WHICH = (K >> 4) & 1;
+    constexpr int XR = ((K & 15) + 1) & 15;
+    constexpr bool PURE = K >= kTileRecKeys;
+    if constexpr (XR < (1 << RB) && !(PURE && XR == 0 && WHICH == 1)) {
+        const double2 *P = tile + ((v0 ^ (unsigned)ca.z) & 0xffu);
+        tile_rec_half<RB, WHICH, XR, 0, PT, PURE>(a, P, v0, rep, ca, cb, s_terms, acc, part);
+        if (XR == 0) tile_rec_half<RB, WHICH, XR, 1, PT, PURE>(a, P, v0, rep, ca, cb, s_terms, acc, part);
+    }
+}
+
+// one dispatch per RUN of equal keys (the records of a batch are sorted by key)
+template <int RB>
+__device__ __forceinline__ void tile_walk_runs(const double2 (&a)[1 << RB], const double2 *__restrict__ tile, unsigned v0, unsigned rep,
+                                               const int4 *__restrict__ s_recs, const double2 *__restrict__ s_terms, double &acc) {
+    int gi = 0;
+    int4 ra = s_recs[0], rb = s_recs[1];
+#pragma unroll 1
+    for (;;) {
+        const unsigned key = (unsigned)ra.z >> 16;
+        if (key >= 2u * kTileRecKeys) break;                          // sentinel
+#define B200VQE_CASE(K)                                                                        \
+        case K:                                                                                \
+            do {                                                                               \
+                const int4 ca = ra, cb = rb;                                                   \
+                ++gi;                                                                          \
+                ra = s_recs[2 * gi];                                                           \
+                rb = s_recs[2 * gi + 1];                                                       \
+                tile_one<RB, K, false>(a, tile, v0, rep, ca, cb, s_terms, acc, nullptr);       \
+            } while (((unsigned)ra.z >> 16) == (unsigned)(K));                                 \
+            break;
+#define B200VQE_CASE8(K) B200VQE_CASE(K) B200VQE_CASE(K + 1) B200VQE_CASE(K + 2) B200VQE_CASE(K + 3) B200VQE_CASE(K + 4) B200VQE_CASE(K + 5) B200VQE_CASE(K + 6) B200VQE_CASE(K + 7)
+        switch (key) {
+            B200VQE_CASE8(0) B200VQE_CASE8(8) B200VQE_CASE8(16) B200VQE_CASE8(24) B200VQE_CASE8(32) B200VQE_CASE8(40) B200VQE_CASE8(48) B200VQE_CASE8(56)
+            default: break;
+        }
+#undef B200VQE_CASE8
+#undef B200VQE_CASE
+    }
+}
+
+template <int RB, bool PT = false>
+__device__ __forceinline__ void tile_switch(const double2 (&a)[1 << RB], const double2 *__restrict__ tile, unsigned v0, unsigned rep,
+                                            const int4 *__restrict__ s_recs, const double2 *__restrict__ s_terms, int n_r, double &acc,
+                                            double *part = nullptr) {
+    int4 ra = s_recs[0], rb = s_recs[1];
+#pragma unroll 1
+    for (int gi = 0; gi < n_r; ++gi) {
+        const int4 ca = ra, cb = rb;
+        ra = s_recs[2 * gi + 2];                                       // next record (or the sentinel)
+        rb = s_recs[2 * gi + 3];
+#define B200VQE_CASE(K) case K: tile_one<RB, K, PT>(a, tile, v0, rep, ca, cb, s_terms, acc, part); break;
+#define B200VQE_CASE8(K) B200VQE_CASE(K) B200VQE_CASE(K + 1) B200VQE_CASE(K + 2) B200VQE_CASE(K + 3) B200VQE_CASE(K + 4) B200VQE_CASE(K + 5) B200VQE_CASE(K + 6) B200VQE_CASE(K + 7)
+        switch ((unsigned)ca.z >> 16) {
+            B200VQE_CASE8(0) B200VQE_CASE8(8) B200VQE_CASE8(16) B200VQE_CASE8(24) B200VQE_CASE8(32) B200VQE_CASE8(40) B200VQE_CASE8(48) B200VQE_CASE8(56)
+            default: break;
+        }
+#undef B200VQE_CASE8
+#undef B200VQE_CASE
     }
 }
 
@@ -219,7 +286,10 @@ __device__ __forceinline__ void prefetch_l2(const void *p) {
 // PT = per-term output (b200vqe_expectation(per_term), RDM): instead of the energy, every CTA leaves the signed pair
 // sums of each term over ITS tiles in term_partials[blockIdx.x][plan term] (per-warp accumulators in shared memory,
 // flushed at every batch switch; fixed order, no atomics); k_sum_term_partials adds the CTAs in order.
-template <int MINB, bool PT = false>
+// DISP = how the records of a batch are dispatched to their specialised loops: 0 chain of key tests over all 64 keys,
+// 1 one jump table per record, 2 chain over the 32 generic keys only (plans without pure records), 3 = 2 without the shear
+// (planner 1 only: the kernel of the first version, kept for A/B measurements)
+template <int MINB, bool PT = false, int DISP = 0>
 __global__ void __launch_bounds__(kBlock, MINB)
 k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_bytes, const TileBatch *__restrict__ batches, int n_batches,
               unsigned long long tile_begin, unsigned long long tile_count, const TileRec *__restrict__ recs,
@@ -300,7 +370,7 @@ k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_byte
         for (int r = 0; r < 16; ++r) {
             const unsigned hi = base ^ ((r & 1) ? rb0 : 0u) ^ ((r & 2) ? rb1 : 0u) ^ ((r & 4) ? rb2 : 0u) ^ ((r & 8) ? rb3 : 0u);
             // register r holds the amplitude with low index bits lo ^ Lambda(r): still one 128-byte line per 8 lanes
-            const unsigned lor = lo_b ^ ((r & 1) ? lm0 : 0u) ^ ((r & 2) ? lm1 : 0u) ^ ((r & 4) ? lm2 : 0u) ^ ((r & 8) ? lm3 : 0u);
+            const unsigned lor = DISP == 3 ? lo_b : (lo_b ^ ((r & 1) ? lm0 : 0u) ^ ((r & 2) ? lm1 : 0u) ^ ((r & 4) ? lm2 : 0u) ^ ((r & 8) ? lm3 : 0u));
             a[r] = __ldcs(reinterpret_cast<const double2 *>(psi_b + ((unsigned long long)hi * chunk_bytes + lor)));   // streamed once per batch
         }
         __syncthreads();                        // readers of the previous tile are done
@@ -317,9 +387,13 @@ k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_byte
                 prefetch_l2(psi_lo + (unsigned long long)(h0 ^ rb0) * chunk_bytes);
             }
         }
-        int gi = 0;
-        int4 ra = s_recs[0], rb = s_recs[1];
-        tile_runs<4, 0, PT>(a, tile, v0, rep, s_recs, s_terms, gi, ra, rb, acc, part);
+        if constexpr (DISP == 1) {
+            tile_switch<4, PT>(a, tile, v0, rep, s_recs, s_terms, sb.r_end - sb.r_begin, acc, part);
+        } else {
+            int gi = 0;
+            int4 ra = s_recs[0], rb = s_recs[1];
+            tile_runs<4, 0, PT, DISP >= 2 ? kTileRecKeys : 2 * kTileRecKeys>(a, tile, v0, rep, s_recs, s_terms, gi, ra, rb, acc, part);
+        }
     }
     if (PT) {
         if (cur_b >= 0) flush_terms();

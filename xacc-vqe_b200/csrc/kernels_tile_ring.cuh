@@ -1,0 +1,489 @@
+// <psi|H|psi> on the tile engine, pipelined:  k_tile_expect_ring.
+//
+// k_tile_expect (kernels_tile.cuh) fills a tile and walks its records in turn: ld.global x16 -> barrier -> STS x16 ->
+// barrier -> walk.  The ncu source page of that kernel puts 46 % of the warp-stall samples into the per-tile code (the
+// first STS waiting for the loads, the two barriers, two integer divisions and the address arithmetic of the 16 loads).
+// Here the fill is taken off the compute warps altogether:
+//
+//   * one CTA per SM, 3 tile buffers of 64 KB in shared memory used as a ring;
+//   * tiles stream from HBM with cp.async.bulk (one bulk copy per 2^C-amplitude chunk, 512 per tile at C = 3, issued by
+//     ONE warp, 16 per lane), completion counted in bytes on the stage's "full" mbarrier;
+//   * TWO groups of 256 threads each own every other tile of the CTA: wait on "full", read their own 16 amplitudes
+//     from the landed tile into registers, walk the batch's records exactly as k_tile_expect does, arrive on the
+//     stage's "empty" mbarrier; the group's first warp then waits for that barrier and streams the CTA's tile i + 3
+//     into the stage just released.  While one group walks tile i and the other tile i+1, tile i+2 is in flight.
+//     (A dedicated 17th producer warp would cost the register budget of four: 96 instead of 128 registers per thread.)
+//
+// The bulk copies land a chunk in its physical order, so the tile sits in shared memory UNsheared: element (row q,
+// thread t) of the sheared layout the records are planned for (tile_plan.hpp, TileBatch::lam) lives at byte
+// (q << 12) | ((t << 4) ^ (Lambda(q) << 4)).  One extra XOR per shared-memory read; pure-register records read nothing.
+//
+// Work items (batch, tile) are visited without divisions: every role advances its own (batch, tile) pair, and the coset
+// representative of the next tile of the same batch is a masked add:  rep' = ((rep | P) + dstep) & ~P  with P the pivot
+// mask of the batch's subspace and dstep the deposited tile stride.
+#pragma once
+#include "kernels_tile.cuh"
+
+namespace b200vqe {
+
+constexpr int kRingStages = 3;
+constexpr int kRingGroups = 2;                                   // consumer groups of kBlock threads
+constexpr int kRingThreads = kRingGroups * kBlock;               // 16 warps x 128 registers = the whole register file
+constexpr int kRingTileBytes = (int)sizeof(double2) << kTileBits;
+
+struct RingTables {                                              // per consumer group
+    TileBatch sb;
+    int4 recs[2 * (kStageRecs + 1)];
+    double2 terms[kStageTerms];
+};
+constexpr int kRingSmemBytes = kRingStages * kRingTileBytes + kRingGroups * (int)sizeof(RingTables) + 2 * kRingStages * 8 + 64 * 8;
+
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    unsigned done;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    } while (!done);
+}
+// global -> shared bulk copy (TMA unit, no tensor map), completion in bytes on an mbarrier
+__device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned bytes, unsigned bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void group_sync(int g) {               // named barrier of one consumer group
+    if (g == 0) asm volatile("bar.sync 1, %0;" ::"n"(kBlock) : "memory");
+    else asm volatile("bar.sync 2, %0;" ::"n"(kBlock) : "memory");
+}
+__device__ __forceinline__ double2 lds_f64x2(unsigned addr) {
+    double2 v;
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(addr));
+    return v;
+}
+
+// Lambda(q) << 4 from the four per-batch generators, q a compile-time constant after unrolling
+__device__ __forceinline__ unsigned shear_bytes(int q, unsigned lm0, unsigned lm1, unsigned lm2, unsigned lm3) {
+    unsigned l = 0;
+    if (q & 1) l ^= lm0;
+    if (q & 2) l ^= lm1;
+    if (q & 4) l ^= lm2;
+    if (q & 8) l ^= lm3;
+    return l;
+}
+
+struct RingShear { unsigned lm0, lm1, lm2, lm3; };
+
+// one half of a record on the ring layout; see tile_rec_half (kernels_tile.cuh) for the arithmetic
+template <int WHICH, int XR, int BV, bool PURE>
+__device__ __forceinline__ void ring_rec_half(const double2 (&a)[16], unsigned Pu, const RingShear &sh, unsigned v0, unsigned rep,
+                                              const int4 ra, const int4 rb, const double2 *__restrict__ s_terms, double &acc) {
+    constexpr int RB = 4;
+    constexpr int HS = XR ? XrInfo<XR>::HS : RB - 1;
+    constexpr int NP = 1 << (RB - 1);
+    double w[NP];
+#pragma unroll
+    for (int i = 0; i < NP; ++i) {
+        const int r = ((i >> HS) << (HS + 1)) | (BV << HS) | (i & ((1 << HS) - 1));
+        const int q = r ^ XR;
+        const double2 b = PURE ? a[q] : lds_f64x2((Pu ^ shear_bytes(q, sh.lm0, sh.lm1, sh.lm2, sh.lm3)) + ((unsigned)q << 12));
+        w[i] = WHICH == 0 ? fma(b.x, a[r].x, b.y * a[r].y) : fma(b.x, a[r].y, -(b.y * a[r].x));
+    }
+    double *none = nullptr;
+    tile_term<RB, HS, BV, false>(w, ((unsigned long long)(unsigned)rb.y << 32) | (unsigned)rb.x, __hiloint2double(rb.w, rb.z), v0, rep, acc, none);
+    const int count = ra.y;
+    if (count > 1) {
+        const double2 *tp = s_terms + ra.x;
+        double2 t = tp[1];
+#pragma unroll 1
+        for (int e = 1; e < count; ++e) {
+            const double2 c = t;
+            if (e + 1 < count) t = tp[e + 1];
+            tile_term<RB, HS, BV, false>(w, (unsigned long long)__double_as_longlong(c.x), c.y, v0, rep, acc, none);
+        }
+    }
+}
+
+template <int K>
+__device__ __forceinline__ void ring_one(const double2 (&a)[16], unsigned tile_u, const RingShear &sh, unsigned v0, unsigned rep,
+                                         const int4 ca, const int4 cb, const double2 *__restrict__ s_terms, double &acc) {
+    constexpr int WHICH = (K >> 4) & 1;
+    constexpr int XR = ((K & 15) + 1) & 15;
+    constexpr bool PURE = K >= kTileRecKeys;
+    if constexpr (!(PURE && XR == 0 && WHICH == 1)) {
+        const unsigned Pu = tile_u + (((v0 ^ (unsigned)ca.z) & 0xffu) << 4);      // row 0 of the partner thread, unsheared
+        ring_rec_half<WHICH, XR, 0, PURE>(a, Pu, sh, v0, rep, ca, cb, s_terms, acc);
+        if (XR == 0) ring_rec_half<WHICH, XR, 1, PURE>(a, Pu, sh, v0, rep, ca, cb, s_terms, acc);
+    }
+}
+
+// all records of the batch: one dispatch per RUN of equal keys (records are sorted by key)
+__device__ __forceinline__ void ring_walk(const double2 (&a)[16], unsigned tile_u, const RingShear &sh, unsigned v0, unsigned rep,
+                                          const int4 *__restrict__ s_recs, const double2 *__restrict__ s_terms, double &acc) {
+    int gi = 0;
+    int4 ra = s_recs[0], rb = s_recs[1];
+#pragma unroll 1
+    for (;;) {
+        const unsigned key = (unsigned)ra.z >> 16;
+        if (key >= 2u * kTileRecKeys) break;                          // sentinel
+#define B200VQE_CASE(K)                                                                        \
+        case K:                                                                                \
+            do {                                                                               \
+                const int4 ca = ra, cb = rb;                                                   \
+                ++gi;                                                                          \
+                ra = s_recs[2 * gi];                                                           \
+                rb = s_recs[2 * gi + 1];                                                       \
+                ring_one<K>(a, tile_u, sh, v0, rep, ca, cb, s_terms, acc);                     \
+            } while (((unsigned)ra.z >> 16) == (unsigned)(K));                                 \
+            break;
+#define B200VQE_CASE8(K) B200VQE_CASE(K) B200VQE_CASE(K + 1) B200VQE_CASE(K + 2) B200VQE_CASE(K + 3) B200VQE_CASE(K + 4) B200VQE_CASE(K + 5) B200VQE_CASE(K + 6) B200VQE_CASE(K + 7)
+        switch (key) {
+            B200VQE_CASE8(0) B200VQE_CASE8(8) B200VQE_CASE8(16) B200VQE_CASE8(24) B200VQE_CASE8(32) B200VQE_CASE8(40) B200VQE_CASE8(48) B200VQE_CASE8(56)
+            default: break;
+        }
+#undef B200VQE_CASE8
+#undef B200VQE_CASE
+    }
+}
+
+// (batch, tile) of a role, advanced without divisions
+struct RingCursor {
+    int b;
+    unsigned long long t;            // tile of batch b, relative to tile_begin
+    __device__ __forceinline__ void advance(unsigned long long step, unsigned long long tile_count) {
+        t += step;
+        while (t >= tile_count) { t -= tile_count; ++b; }
+    }
+};
+
+// One warp streams tile (b, t) into stage s: 512 bulk copies of 128 B (16 per lane), bytes counted on full[s].
+// Chunk (k << 5 | lane) of the tile = high index  rep ^ XOR_i mu_i basis[i]  with mu = k << 5 | lane.
+__device__ __forceinline__ void ring_fill(const double2 *__restrict__ psi, const TileBatch *__restrict__ B, int M, unsigned t_abs,
+                                          unsigned tile_u, unsigned full_bar, int lane) {
+    constexpr int C = 3;
+    unsigned rep = 0;
+#pragma unroll
+    for (int i = 0; i <= kTileMaxDim; ++i) rep |= (t_abs & __ldg(&B->seg[i])) << i;
+    unsigned base = rep;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) if ((lane >> k) & 1) base ^= __ldg(&B->basis[k]);       // chunk coordinate bits 0..4 = lane
+    const unsigned kb0 = __ldg(&B->basis[5]), kb1 = __ldg(&B->basis[6]), kb2 = __ldg(&B->basis[7]), kb3 = M > 8 ? __ldg(&B->basis[8]) : 0u;
+    if (lane == 0) mbar_arrive_expect_tx(full_bar, (unsigned)kRingTileBytes);
+    __syncwarp();
+    const char *psi_b = reinterpret_cast<const char *>(psi);
+    const unsigned dst0 = tile_u + ((unsigned)lane << (C + 4));
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        const unsigned hi = base ^ ((k & 1) ? kb0 : 0u) ^ ((k & 2) ? kb1 : 0u) ^ ((k & 4) ? kb2 : 0u) ^ ((k & 8) ? kb3 : 0u);
+        bulk_g2s(dst0 + ((unsigned)k << (5 + C + 4)), psi_b + ((unsigned long long)hi << (C + 4)), 16u << C, full_bar);
+    }
+}
+
+// C == 3 only (128-byte chunks); grid = number of SMs; dynamic shared memory = kRingSmemBytes.
+// Item i of a CTA (its i-th (batch, tile) pair) lives in stage i % 3 and is walked by group i % 2; when a group has
+// finished item i, its first warp waits for the stage to be released by the whole group and streams item i + 3 into it.
+__global__ void __launch_bounds__(kRingThreads, 1)
+k_tile_expect_ring(const double2 *__restrict__ psi, int M, const TileBatch *__restrict__ batches, int n_batches,
+                   unsigned long long tile_begin, unsigned long long tile_count, const TileRec *__restrict__ recs,
+                   const TileTerm *__restrict__ terms, double *partials, unsigned *counter, double *out) {
+    extern __shared__ __align__(128) unsigned char ring_raw[];
+    unsigned char *tiles = ring_raw;                                                     // [kRingStages][64 KB]
+    RingTables *tabs = reinterpret_cast<RingTables *>(ring_raw + kRingStages * kRingTileBytes);
+    unsigned long long *bars = reinterpret_cast<unsigned long long *>(tabs + kRingGroups);   // full[3], empty[3]
+    double *s_red = reinterpret_cast<double *>(bars + 2 * kRingStages);                   // [16] warp sums
+    const unsigned tiles_u = smem_u32(tiles);
+    const unsigned full_u = smem_u32(bars), empty_u = smem_u32(bars + kRingStages);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kRingStages; ++s) {
+            mbar_init(full_u + 8 * s, 1);                     // the filling warp's arrive.expect_tx; the copies complete the bytes
+            mbar_init(empty_u + 8 * s, kBlock / 32);          // one arrive per warp of the group that walked the stage
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+
+    const unsigned long long total = (unsigned long long)n_batches * tile_count;
+    const unsigned long long n_items = blockIdx.x < total ? (total - blockIdx.x + gridDim.x - 1) / gridDim.x : 0ull;   // once per kernel
+    const int g = warp / (kBlock / 32);
+    const bool leader = (warp % (kBlock / 32)) == 0;
+    const unsigned v0 = threadIdx.x & (kBlock - 1);
+    RingTables &tb = tabs[g];
+    const unsigned long long step = (unsigned long long)kRingGroups * gridDim.x;
+    double acc = 0.0;
+
+    RingCursor fill{0, 0};              // next item this group's first warp streams in (item g + 3 after the prologue)
+    if (leader) {
+        // prologue: items 0 and 2 by group 0, item 1 by group 1
+        for (int j = g; j < kRingStages; j += kRingGroups) {
+            if ((unsigned long long)j < n_items) {
+                RingCursor c{0, 0};
+                c.advance(blockIdx.x + (unsigned long long)j * gridDim.x, tile_count);
+                ring_fill(psi, batches + c.b, M, (unsigned)(tile_begin + c.t), tiles_u + (unsigned)j * kRingTileBytes, full_u + 8 * j, lane);
+            }
+        }
+        fill.advance(blockIdx.x + (unsigned long long)(g + kRingStages) * gridDim.x, tile_count);
+    }
+
+    RingCursor cur{0, 0};
+    cur.advance(blockIdx.x + (unsigned long long)g * gridDim.x, tile_count);
+    int cur_b = -1;
+    unsigned piv = 0, dstep = 0, rep = 0;
+    RingShear sh{0, 0, 0, 0};
+    int s = g;                                              // stage of item i = i % kRingStages, use u = i / kRingStages
+    unsigned u = 0;
+    for (unsigned long long i = g; i < n_items; i += kRingGroups) {
+        if (cur.b != cur_b) {                               // uniform over the group
+            cur_b = cur.b;
+            group_sync(g);                                  // everyone is done with the previous batch's tables
+            if (v0 < kTileBatchWords) reinterpret_cast<uint32_t *>(&tb.sb)[v0] = reinterpret_cast<const uint32_t *>(&batches[cur_b])[v0];
+            group_sync(g);
+            const int n_r = tb.sb.r_end - tb.sb.r_begin, n_t = tb.sb.t_end - tb.sb.t_begin;
+            const int4 *rsrc = reinterpret_cast<const int4 *>(recs + tb.sb.r_begin);
+            for (int k = (int)v0; k < 2 * n_r; k += kBlock) {
+                int4 q = rsrc[k];
+                if (!(k & 1)) q.x -= tb.sb.t_begin;
+                tb.recs[k] = q;
+            }
+            if (v0 == 0) tb.recs[2 * n_r] = make_int4(0, 0, 0xff << 16, 0);
+            const double2 *tsrc = reinterpret_cast<const double2 *>(terms) + tb.sb.t_begin;
+            for (int k = (int)v0; k < n_t; k += kBlock) tb.terms[k] = tsrc[k];
+            sh.lm0 = tb.sb.lam[0] << 4; sh.lm1 = tb.sb.lam[1] << 4; sh.lm2 = tb.sb.lam[2] << 4; sh.lm3 = tb.sb.lam[3] << 4;
+            piv = tb.sb.pad[0];
+            dstep = tile_rep(tb.sb, (unsigned)step);
+            group_sync(g);
+            rep = tile_rep(tb.sb, (unsigned)(tile_begin + cur.t));
+        }
+        mbar_wait(full_u + 8 * s, u & 1u);                  // the tile has landed
+        const unsigned tile_u = tiles_u + (unsigned)s * kRingTileBytes;
+        double2 a[16];
+        const unsigned own = tile_u + (v0 << 4);
+#pragma unroll
+        for (int r = 0; r < 16; ++r) a[r] = lds_f64x2((own ^ shear_bytes(r, sh.lm0, sh.lm1, sh.lm2, sh.lm3)) + ((unsigned)r << 12));
+        ring_walk(a, tile_u, sh, v0, rep, tb.recs, tb.terms, acc);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty_u + 8 * s);       // release: this warp's reads of the stage are complete
+        if (leader && i + kRingStages < n_items) {
+            mbar_wait(empty_u + 8 * s, u & 1u);            // ... and so are the other warps' of the group
+            ring_fill(psi, batches + fill.b, M, (unsigned)(tile_begin + fill.t), tile_u, full_u + 8 * s, lane);
+            fill.advance(step, tile_count);
+        }
+        // next tile of this group: same batch -> masked add of the deposited stride (a new batch recomputes it above)
+        cur.advance(step, tile_count);
+        rep = ((rep | piv) + dstep) & ~piv;
+        s += kRingGroups;
+        if (s >= kRingStages) { s -= kRingStages; ++u; }
+    }
+    const double wsum = warp_sum(acc);
+    if (lane == 0) s_red[warp] = wsum;
+    __syncthreads();
+    // deterministic grid reduction: per-CTA sum in warp order, the last CTA adds the CTAs in order
+    __shared__ bool s_last;
+    if (threadIdx.x == 0) {
+        double sum = 0.0;
+#pragma unroll
+        for (int w = 0; w < kRingGroups * (kBlock / 32); ++w) sum += s_red[w];
+        partials[blockIdx.x] = sum;
+        __threadfence();
+        s_last = atomicAdd(counter, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (s_last && threadIdx.x < 32) {
+        __threadfence();
+        double sum = 0.0;
+        for (unsigned b = lane; b < gridDim.x; b += 32) sum += __ldcg(&partials[b]);
+        sum = warp_sum(sum);
+        if (lane == 0) { out[0] = sum; *counter = 0u; }
+    }
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// The same ring filled with cp.async (LDGSTS, 16 B per thread) instead of bulk copies: k_tile_expect_pipe, the default.
+//
+// Why: cp.async.bulk compiles to UBLKCP, a UNIFORM-datapath instruction -- one copy per warp-instruction, its operands in
+// uniform registers.  A warp whose lanes hold 32 different chunk addresses is serialised by the compiler into an
+// ELECT / 4 x R2UR.BROADCAST / UBLKCP / BRA.U.ANY loop (see the SASS of k_tile_expect_ring): ~9 issue slots per 128-byte
+// chunk, 512 chunks per tile = ~4600 warp-instructions per tile, against 128 LDGSTS warp-instructions (+ addresses) for
+// the same 64 KB.  The cosets of a GF(2) subspace are XOR-scattered 128-byte chunks, so there is no larger contiguous
+// run for a bulk copy and no affine tensor map that describes a tile.
+//
+// Every thread copies exactly the 16 amplitudes it owns, so the tile lands in the SHEARED (thread, register) layout the
+// records are planned for and the walk is the plain code of kernels_tile.cuh (partner rows at immediate offsets).
+// Completion is still an mbarrier per stage: every copying thread issues cp.async.mbarrier.arrive.noinc on full[s].
+// The group that walked item i is the one that refills its stage with item i + 3 (after a barrier of that group only),
+// so no "empty" barrier is needed: group 0 streams the odd items, group 1 the even ones.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async_arrive_noinc(unsigned bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void cp_async16_u(unsigned dst, const void *src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+
+struct PipeFillBatch {               // what a fill needs of its batch (shared memory, per group)
+    uint32_t basis[kTileMaxDim];
+    uint32_t seg[kTileMaxDim + 1];
+    uint32_t lam[4];
+    uint32_t piv;
+    uint32_t pad[6];
+};
+constexpr int kPipeSmemBytes = kRingStages * kRingTileBytes + kRingGroups * (int)(sizeof(RingTables) + sizeof(PipeFillBatch)) + kRingStages * 8 + 32 * 8;
+
+__global__ void __launch_bounds__(kRingThreads, 1)
+k_tile_expect_pipe(const double2 *__restrict__ psi, int C, int M, const TileBatch *__restrict__ batches, int n_batches,
+                   unsigned long long tile_begin, unsigned long long tile_count, const TileRec *__restrict__ recs,
+                   const TileTerm *__restrict__ terms, double *partials, unsigned *counter, double *out) {
+    extern __shared__ __align__(128) unsigned char ring_raw[];
+    unsigned char *tiles = ring_raw;                                                     // [kRingStages][64 KB]
+    RingTables *tabs = reinterpret_cast<RingTables *>(ring_raw + kRingStages * kRingTileBytes);
+    PipeFillBatch *fbs = reinterpret_cast<PipeFillBatch *>(tabs + kRingGroups);
+    unsigned long long *bars = reinterpret_cast<unsigned long long *>(fbs + kRingGroups);    // full[3]
+    double *s_red = reinterpret_cast<double *>(bars + kRingStages);                       // [16] warp sums
+    const unsigned tiles_u = smem_u32(tiles);
+    const unsigned full_u = smem_u32(bars);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kRingStages; ++s) mbar_init(full_u + 8 * s, kBlock);      // one (noinc) arrive per copying thread
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    const unsigned long long total = (unsigned long long)n_batches * tile_count;
+    const unsigned long long n_items = blockIdx.x < total ? (total - blockIdx.x + gridDim.x - 1) / gridDim.x : 0ull;   // once per kernel
+    const int g = warp / (kBlock / 32);
+    const unsigned v0 = threadIdx.x & (kBlock - 1);
+    const unsigned lo_b = (v0 & ((1u << C) - 1u)) << 4;
+    const unsigned chunk_shift = (unsigned)C + 4u;
+    RingTables &tb = tabs[g];
+    PipeFillBatch &fb = fbs[g];
+    const unsigned long long step = (unsigned long long)kRingGroups * gridDim.x;
+    const char *psi_b = reinterpret_cast<const char *>(psi);
+    double acc = 0.0;
+
+    // ---- fill side: this group streams items 1 - g, 3 - g, 5 - g, ... (stage = item % 3) ----
+    RingCursor fcur{0, 0};
+    fcur.advance(blockIdx.x + (unsigned long long)(1 - g) * gridDim.x, tile_count);
+    unsigned long long fi = (unsigned long long)(1 - g);
+    int fs = 1 - g;
+    int f_b = -1;
+    unsigned f_rep = 0, f_dstep = 0, f_tc = 0;
+    auto fill_one = [&]() {                              // all 256 threads of the group
+        if (fcur.b != f_b) {
+            f_b = fcur.b;
+            group_sync(g);                               // earlier fills have read the previous descriptor
+            const TileBatch *B = batches + f_b;
+            if (v0 < kTileMaxDim) fb.basis[v0] = B->basis[v0];
+            else if (v0 < 2 * kTileMaxDim + 1) fb.seg[v0 - kTileMaxDim] = B->seg[v0 - kTileMaxDim];
+            else if (v0 < 2 * kTileMaxDim + 5) fb.lam[v0 - 2 * kTileMaxDim - 1] = B->lam[v0 - 2 * kTileMaxDim - 1];
+            else if (v0 == 2 * kTileMaxDim + 5) fb.piv = B->pad[0];
+            group_sync(g);
+            f_tc = 0;
+            for (int k = 0; k < 8 - C; ++k) if ((v0 >> (C + k)) & 1u) f_tc ^= fb.basis[k];
+            unsigned r0 = 0, d0 = 0;
+            const unsigned t_abs = (unsigned)(tile_begin + fcur.t), st = (unsigned)step;
+#pragma unroll
+            for (int k = 0; k <= kTileMaxDim; ++k) { r0 |= (t_abs & fb.seg[k]) << k; d0 |= (st & fb.seg[k]) << k; }
+            f_rep = r0; f_dstep = d0;
+        }
+        const unsigned rb0 = fb.basis[M - 4], rb1 = fb.basis[M - 3], rb2 = fb.basis[M - 2], rb3 = fb.basis[M - 1];
+        const unsigned lm0 = fb.lam[0] << 4, lm1 = fb.lam[1] << 4, lm2 = fb.lam[2] << 4, lm3 = fb.lam[3] << 4;
+        const unsigned base = f_rep ^ f_tc;
+        const unsigned dst = tiles_u + (unsigned)fs * kRingTileBytes + (v0 << 4);
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+            const unsigned hi = base ^ ((r & 1) ? rb0 : 0u) ^ ((r & 2) ? rb1 : 0u) ^ ((r & 4) ? rb2 : 0u) ^ ((r & 8) ? rb3 : 0u);
+            const unsigned lor = lo_b ^ ((r & 1) ? lm0 : 0u) ^ ((r & 2) ? lm1 : 0u) ^ ((r & 4) ? lm2 : 0u) ^ ((r & 8) ? lm3 : 0u);
+            cp_async16_u(dst + ((unsigned)r << 12), psi_b + (((unsigned long long)hi << chunk_shift) + lor));
+        }
+        cp_async_arrive_noinc(full_u + 8 * fs);
+        // next item of this group's fill sequence: same batch -> masked add of the deposited stride
+        fcur.advance(step, tile_count);
+        f_rep = ((f_rep | fb.piv) + f_dstep) & ~fb.piv;
+        fi += kRingGroups;
+        fs += kRingGroups;
+        if (fs >= kRingStages) fs -= kRingStages;
+    };
+    // prologue: items 0, 1, 2
+    if (fi < n_items) fill_one();
+    if (g == 1 && fi < n_items) fill_one();
+
+    // ---- walk side: this group owns items g, g + 2, ... ----
+    RingCursor cur{0, 0};
+    cur.advance(blockIdx.x + (unsigned long long)g * gridDim.x, tile_count);
+    int cur_b = -1;
+    unsigned piv = 0, dstep = 0, rep = 0;
+    int s = g;                                              // stage of item i = i % kRingStages, use u = i / kRingStages
+    unsigned u = 0;
+    for (unsigned long long i = g; i < n_items; i += kRingGroups) {
+        if (cur.b != cur_b) {                               // uniform over the group
+            cur_b = cur.b;
+            group_sync(g);                                  // everyone is done with the previous batch's tables
+            if (v0 < kTileBatchWords) reinterpret_cast<uint32_t *>(&tb.sb)[v0] = reinterpret_cast<const uint32_t *>(&batches[cur_b])[v0];
+            group_sync(g);
+            const int n_r = tb.sb.r_end - tb.sb.r_begin, n_t = tb.sb.t_end - tb.sb.t_begin;
+            const int4 *rsrc = reinterpret_cast<const int4 *>(recs + tb.sb.r_begin);
+            for (int k = (int)v0; k < 2 * n_r; k += kBlock) {
+                int4 q = rsrc[k];
+                if (!(k & 1)) q.x -= tb.sb.t_begin;
+                tb.recs[k] = q;
+            }
+            if (v0 == 0) tb.recs[2 * n_r] = make_int4(0, 0, 0xff << 16, 0);
+            const double2 *tsrc = reinterpret_cast<const double2 *>(terms) + tb.sb.t_begin;
+            for (int k = (int)v0; k < n_t; k += kBlock) tb.terms[k] = tsrc[k];
+            piv = tb.sb.pad[0];
+            dstep = tile_rep(tb.sb, (unsigned)step);
+            group_sync(g);
+            rep = tile_rep(tb.sb, (unsigned)(tile_begin + cur.t));
+        }
+        mbar_wait(full_u + 8 * s, u & 1u);                  // the tile has landed (all 256 copying threads' cp.async are complete)
+        const double2 *tile = reinterpret_cast<const double2 *>(tiles + (size_t)s * kRingTileBytes);
+        double2 a[16];
+#pragma unroll
+        for (int r = 0; r < 16; ++r) a[r] = tile[((unsigned)r << 8) | v0];
+        tile_walk_runs<4>(a, tile, v0, rep, tb.recs, tb.terms, acc);
+        // the stage is refilled by this same group: a barrier of the group is all the release it needs
+        if (i + kRingStages < n_items) {
+            group_sync(g);
+            fill_one();                                     // item i + 3 -> stage s
+        }
+        cur.advance(step, tile_count);
+        rep = ((rep | piv) + dstep) & ~piv;
+        s += kRingGroups;
+        if (s >= kRingStages) { s -= kRingStages; ++u; }
+    }
+    const double wsum = warp_sum(acc);
+    if (lane == 0) s_red[warp] = wsum;
+    __syncthreads();
+    // deterministic grid reduction: per-CTA sum in warp order, the last CTA adds the CTAs in order
+    __shared__ bool s_last;
+    if (threadIdx.x == 0) {
+        double sum = 0.0;
+#pragma unroll
+        for (int w = 0; w < kRingGroups * (kBlock / 32); ++w) sum += s_red[w];
+        partials[blockIdx.x] = sum;
+        __threadfence();
+        s_last = atomicAdd(counter, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (s_last && threadIdx.x < 32) {
+        __threadfence();
+        double sum = 0.0;
+        for (unsigned b = lane; b < gridDim.x; b += 32) sum += __ldcg(&partials[b]);
+        sum = warp_sum(sum);
+        if (lane == 0) { out[0] = sum; *counter = 0u; }
+    }
+}
+
+}  // namespace b200vqe

@@ -46,7 +46,7 @@ struct TileBatch {                   // 160 bytes
     int32_t r_begin, r_end;          // TileRec range of this batch (expectation engine; see build_tile_records)
     uint32_t lam[4];                 // shear: register r of a thread holds the amplitude with low index bits lo ^ Lambda(r),
                                      // Lambda(r) = XOR of lam[k] over the set bits k of r (0 for plans built without shear)
-    uint32_t pad[4];
+    uint32_t pad[4];                 // pad[0] = pivot mask of the subspace (bits of the high index the tile number skips)
 };
 constexpr int kTileBatchWords = 40;
 static_assert(sizeof(TileBatch) == 4 * kTileBatchWords, "TileBatch layout");
@@ -443,6 +443,7 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
             B.basis[i] = (uint32_t)v;
         }
         for (int k = 0; k < 4; ++k) B.lam[k] = lam[k];
+        for (int p : rr.piv) B.pad[0] |= 1u << p;      // pivot mask: the coset representative of tile t + s is ((rep | pad[0]) + deposit(s)) & ~pad[0]
         auto shear_of = [&](unsigned reg) {        // Lambda(reg)
             uint32_t l = 0;
             for (int k = 0; k < RB; ++k) if ((reg >> k) & 1) l ^= lam[k];
