@@ -331,6 +331,92 @@ __device__ __forceinline__ void cp_async16_u(unsigned dst, const void *src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
 }
 
+__device__ __forceinline__ int4 lds_i4(unsigned addr) {
+    int4 v;
+    asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
+
+// One half of a record, lean form: every shared-memory operand is a 32-bit shared address (no generic-pointer
+// arithmetic to rematerialise), the second half of the record descriptor is fetched inside the body, and the partner
+// amplitudes arrive four at a time so that 8 x 4 load registers are never live at once.
+template <int WHICH, int XR, int BV, bool PURE>
+__device__ __forceinline__ void pipe_rec_half(const double2 (&a)[16], unsigned Pu, unsigned v0, unsigned rep, unsigned rec_u, int kb, int count,
+                                              unsigned terms_u, double &acc) {
+    constexpr int RB = 4;
+    constexpr int HS = XR ? XrInfo<XR>::HS : RB - 1;
+    constexpr int NP = 1 << (RB - 1);
+    const int4 rb = lds_i4(rec_u + 16);                 // first term inline: packed z parts, coefficient
+    double w[NP];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        double2 b[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int i = 4 * h + k;
+            const int r = ((i >> HS) << (HS + 1)) | (BV << HS) | (i & ((1 << HS) - 1));
+            b[k] = PURE ? a[r ^ XR] : lds_f64x2(Pu + ((unsigned)(r ^ XR) << 12));
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int i = 4 * h + k;
+            const int r = ((i >> HS) << (HS + 1)) | (BV << HS) | (i & ((1 << HS) - 1));
+            w[i] = WHICH == 0 ? fma(b[k].x, a[r].x, b[k].y * a[r].y) : fma(b[k].x, a[r].y, -(b[k].y * a[r].x));
+        }
+    }
+    double *none = nullptr;
+    tile_term<RB, HS, BV, false>(w, ((unsigned long long)(unsigned)rb.y << 32) | (unsigned)rb.x, __hiloint2double(rb.w, rb.z), v0, rep, acc, none);
+    if (count > 1) {
+        unsigned tu = terms_u + ((unsigned)kb << 4);
+#pragma unroll 1
+        for (int e = 1; e < count; ++e) {
+            tu += 16;
+            const double2 c = lds_f64x2(tu);
+            tile_term<RB, HS, BV, false>(w, (unsigned long long)__double_as_longlong(c.x), c.y, v0, rep, acc, none);
+        }
+    }
+}
+
+template <int K>
+__device__ __forceinline__ void pipe_one(const double2 (&a)[16], unsigned tile_u, unsigned v0, unsigned rep, const int4 ra, unsigned rec_u,
+                                         unsigned terms_u, double &acc) {
+    constexpr int WHICH = (K >> 4) & 1;
+    constexpr int XR = ((K & 15) + 1) & 15;
+    constexpr bool PURE = K >= kTileRecKeys;
+    if constexpr (!(PURE && XR == 0 && WHICH == 1)) {
+        const unsigned Pu = tile_u + (((v0 ^ (unsigned)ra.z) & 0xffu) << 4);      // row 0 of the partner thread
+        pipe_rec_half<WHICH, XR, 0, PURE>(a, Pu, v0, rep, rec_u, ra.x, ra.y, terms_u, acc);
+        if (XR == 0) pipe_rec_half<WHICH, XR, 1, PURE>(a, Pu, v0, rep, rec_u, ra.x, ra.y, terms_u, acc);
+    }
+}
+
+// all records of the batch: one dispatch per RUN of equal keys (records are sorted by key)
+__device__ __forceinline__ void pipe_walk(const double2 (&a)[16], unsigned tile_u, unsigned v0, unsigned rep, unsigned recs_u, unsigned terms_u,
+                                          double &acc) {
+    unsigned ru = recs_u;
+    int4 ra = lds_i4(ru);
+#pragma unroll 1
+    for (;;) {
+        const unsigned key = (unsigned)ra.z >> 16;
+        if (key >= 2u * kTileRecKeys) break;                          // sentinel
+#define B200VQE_CASE(K)                                                                        \
+        case K:                                                                                \
+            do {                                                                               \
+                pipe_one<K>(a, tile_u, v0, rep, ra, ru, terms_u, acc);                         \
+                ru += 32;                                                                      \
+                ra = lds_i4(ru);                                                               \
+            } while (((unsigned)ra.z >> 16) == (unsigned)(K));                                 \
+            break;
+#define B200VQE_CASE8(K) B200VQE_CASE(K) B200VQE_CASE(K + 1) B200VQE_CASE(K + 2) B200VQE_CASE(K + 3) B200VQE_CASE(K + 4) B200VQE_CASE(K + 5) B200VQE_CASE(K + 6) B200VQE_CASE(K + 7)
+        switch (key) {
+            B200VQE_CASE8(0) B200VQE_CASE8(8) B200VQE_CASE8(16) B200VQE_CASE8(24) B200VQE_CASE8(32) B200VQE_CASE8(40) B200VQE_CASE8(48) B200VQE_CASE8(56)
+            default: break;
+        }
+#undef B200VQE_CASE8
+#undef B200VQE_CASE
+    }
+}
+
 struct PipeFillBatch {               // what a fill needs of its batch (shared memory, per group)
     uint32_t basis[kTileMaxDim];
     uint32_t seg[kTileMaxDim + 1];
@@ -368,6 +454,7 @@ k_tile_expect_pipe(const double2 *__restrict__ psi, int C, int M, const TileBatc
     const unsigned chunk_shift = (unsigned)C + 4u;
     RingTables &tb = tabs[g];
     PipeFillBatch &fb = fbs[g];
+    const unsigned recs_u = smem_u32(tb.recs), terms_u = smem_u32(tb.terms);
     const unsigned long long step = (unsigned long long)kRingGroups * gridDim.x;
     const char *psi_b = reinterpret_cast<const char *>(psi);
     double acc = 0.0;
@@ -448,11 +535,11 @@ k_tile_expect_pipe(const double2 *__restrict__ psi, int C, int M, const TileBatc
             rep = tile_rep(tb.sb, (unsigned)(tile_begin + cur.t));
         }
         mbar_wait(full_u + 8 * s, u & 1u);                  // the tile has landed (all 256 copying threads' cp.async are complete)
-        const double2 *tile = reinterpret_cast<const double2 *>(tiles + (size_t)s * kRingTileBytes);
+        const unsigned tile_u = tiles_u + (unsigned)s * kRingTileBytes;
         double2 a[16];
 #pragma unroll
-        for (int r = 0; r < 16; ++r) a[r] = tile[((unsigned)r << 8) | v0];
-        tile_walk_runs<4>(a, tile, v0, rep, tb.recs, tb.terms, acc);
+        for (int r = 0; r < 16; ++r) a[r] = lds_f64x2(tile_u + (v0 << 4) + ((unsigned)r << 12));
+        pipe_walk(a, tile_u, v0, rep, recs_u, terms_u, acc);
         // the stage is refilled by this same group: a barrier of the group is all the release it needs
         if (i + kRingStages < n_items) {
             group_sync(g);
