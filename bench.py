@@ -1,13 +1,13 @@
 #!/usr/bin/env python
 """bench.py -- headline benchmark of the hot path (BASELINE.json: term.amplitude updates/s).
 
-Workload at N = 1 (configs[3]): synthetic 28-qubit random Pauli sum, 10^4 terms, fp64
-<psi|H|psi>.  A step is one full <psi|H|psi> over all terms.  At N > 1 the register grows by
-log2(N) qubits (weak scaling: 2^28 amplitudes per GPU), sharded by the high index bits.
+Workload at N = 1 (configs[3]): synthetic 28-qubit random Pauli sum, 10^4 terms, fp64 <psi|H|psi>.  A step is one full
+<psi|H|psi> over all terms.  At N > 1 the register grows by log2(N) qubits (weak scaling: 2^28 amplitudes per GPU), sharded
+by the high index bits.  The same JSON line also carries H psi and one Lanczos step on the same operator (`extra`).
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
 
-Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for every field.
+Prints ONE JSON line (rank 0); exits non-zero when a correctness guard fails.  See DESIGN.md "Measurement" for every field.
 """
 from __future__ import annotations
 
@@ -23,15 +23,14 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-# NCCL writes its banner ("NCCL version ...") to stdout at NCCL_DEBUG=VERSION/INFO; stdout carries exactly one JSON line
-if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION", "INFO"):
-    os.environ["NCCL_DEBUG"] = "WARN"
 
 METRIC = "H.psi term.amplitude updates/s"
 UNIT = "updates/s"
 N_QUBITS_1GPU = 28
 N_TERMS = 10_000
 SEED = 28
+GUARD_TOL = 1e-10          # north_star: energies to 1e-10 relative
+NVLINK_NOMINAL_GBS, NVLINK_MEASURED_GBS = 900.0, 770.0     # per direction per GPU (B200_PROFILING.md)
 
 
 def synth_pauli_sum(n: int, n_terms: int, seed: int):
@@ -118,17 +117,30 @@ def measured_peak_gbs():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def host_cores() -> int:
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def load_oracle():
+    """The C/OpenMP oracle with every host core: torchrun exports OMP_NUM_THREADS=1, which must not reach the CPU arm."""
+    os.environ["OMP_NUM_THREADS"] = str(host_cores())
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import c_oracle as co
+    co.lib()
+    return co
+
+
 _CPU_PSI = {}
 
 
-def cpu_baseline(n: int, xm, zm, cf, n_sample_terms: int):
-    """The oracle (C/OpenMP mask-based port of the reference algorithm) timed on the host cores on a
-    bounded sample: the same register size, the first `n_sample_terms` terms."""
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    import c_oracle as co
-    N = 1 << n
+def host_random_state(n: int):
+    """Normalised complex Gaussian on the host (seeded per 2^24 block), cached: the CPU arm and the GPU cross-check share it."""
     psi = _CPU_PSI.get(n)
-    if psi is None:                      # the reference arm times several samples on the same state
+    if psi is None:
+        N = 1 << n
         rng = np.random.default_rng(SEED)
         psi = np.empty(N, dtype=np.complex128)
         blk = 1 << 24
@@ -138,26 +150,54 @@ def cpu_baseline(n: int, xm, zm, cf, n_sample_terms: int):
         psi *= 1.0 / np.sqrt(2.0 * N)
         _CPU_PSI.clear()
         _CPU_PSI[n] = psi
+    return psi
+
+
+def cpu_baseline(co, n: int, xm, zm, cf, n_sample_terms: int):
+    """The oracle (C/OpenMP mask-based port of the reference algorithm) timed on the host cores on a
+    bounded sample: the same register size, the first `n_sample_terms` terms.  Returns (record, seconds, k, energy)."""
+    N = 1 << n
+    psi = host_random_state(n)
     k = min(n_sample_terms, len(xm))
     co.expect(n, xm[:1], zm[:1], cf[:1], psi)          # warm up threads / page in
     t0 = time.perf_counter()
-    co.expect(n, xm[:k], zm[:k], cf[:k], psi)
+    e, _ = co.expect(n, xm[:k], zm[:k], cf[:k], psi)
     dt = time.perf_counter() - t0
-    return {"value": k * N / dt, "unit": UNIT, "cores": co.num_threads(), "kind": "port",
-            "sample": f"{k} of {len(xm)} terms on the full 2^{n} register, C/OpenMP mask-based oracle (oracle/hpsi_oracle.c), {dt:.2f} s"}, dt, k
+    return ({"value": k * N / dt, "unit": UNIT, "cores": co.num_threads(), "kind": "port",
+             "sample": f"{k} of {len(xm)} terms on the full 2^{n} register, C/OpenMP mask-based oracle (oracle/hpsi_oracle.c), {dt:.2f} s"},
+            dt, k, e)
+
+
+def mem_available_bytes() -> int:
+    try:
+        with open("/proc/meminfo") as f:
+            for line in f:
+                if line.startswith("MemAvailable:"):
+                    return int(line.split()[1]) * 1024
+    except Exception:
+        pass
+    return 32 << 30
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    n = N_QUBITS_1GPU       # host RAM bounds the CPU arm to the 1-GPU register
-    xm, zm, cf, _ = synth_pauli_sum(n, N_TERMS, SEED)
-    sample_terms = args.cpu_terms
+    co = load_oracle()
+    # the GPU arm grows the register with the GPU count (weak scaling); the CPU arm follows while the host RAM holds the state
+    wl = int(np.log2(max(1, args.gpus)))
+    n = args.qubits + wl
+    cap = ""
+    while n > args.qubits and (16 << n) > 0.6 * mem_available_bytes():
+        n -= 1
+        cap = f"; register capped at {n} qubits by host RAM"
+    xm, zm, cf, _ = synth_pauli_sum(n, args.terms, SEED)
+    # the same ~15-30 s of CPU work per step at every size
+    sample_terms = max(2, args.cpu_terms >> (n - args.qubits))
     vals, times = [], []
     base = None
     for i in range(args.warmup + args.steps):
-        base, dt, k = cpu_baseline(n, xm, zm, cf, sample_terms) if i == 0 or True else (base, 0, 0)
+        base, dt, k, _ = cpu_baseline(co, n, xm, zm, cf, sample_terms)
         if i >= args.warmup:
             vals.append(base["value"])
             times.append(dt)
@@ -168,11 +208,65 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * float(np.mean(times)), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"synthetic {n}-qubit random Pauli sum, {len(xm)} terms, fp64 <psi|H|psi> (bounded sample of terms per step)",
+            "config": {"workload": f"synthetic {n}-qubit random Pauli sum, {len(xm)} terms, fp64 <psi|H|psi> (bounded sample of terms per step{cap})",
                        "n_qubits": n, "n_terms": int(len(xm))},
             "cpu_baseline": base,
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit(line)
+
+
+def sharded_parity_check(xb, dist, torch, rank, world, local_rank):
+    """N >= 2 only: H psi, <psi|H|psi> and a short Lanczos run of a SHARDED small register against the CPU oracle, so that every
+    multi-GPU driver run exercises the exchange paths (the pytest multi-GPU cases skip on a 1-GPU box)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import c_oracle as co
+    wl = int(np.log2(world))
+    n = 18 + wl
+    ids = [xb.Backend.comm_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(ids, src=0)
+    be = xb.Backend(n, device=local_rank, rank=rank, world=world, comm_id=ids[0])
+    be.n_slots(3)
+    xm, zm, cf, _ = synth_pauli_sum(n, 96, SEED + 7)
+    be.set_option("apply-engine", "tile")
+    be.set_hamiltonian(xm, zm, cf)
+    rng = np.random.default_rng(SEED + 8)
+    psi = rng.normal(size=1 << n) + 1j * rng.normal(size=1 << n)
+    psi /= np.linalg.norm(psi)
+    lo, hi = be.first, be.first + be.n_local
+    be.upload(psi[lo:hi])
+    scale = float(np.abs(cf).sum())
+    e = be.expectation()
+    be.apply_h(0, 1, want_alpha=False)
+    got = be.download(1)
+    out = {}
+    if rank == 0:
+        eo, _ = co.expect(n, xm, zm, cf, psi)
+        out["expect_rel_err"] = abs(e - eo) / max(abs(eo), 1e-300)
+        out["expect_err_over_sum_abs_c"] = abs(e - eo) / scale
+    want = co.apply(n, xm, zm, cf, psi)[lo:hi]
+    err = torch.tensor([float(np.abs(got - want).max()) / scale], dtype=torch.float64, device="cuda")
+    dist.all_reduce(err, op=dist.ReduceOp.MAX)
+    out["apply_max_err_over_sum_abs_c"] = float(err.item())
+    # Lanczos on a block-decoupled operator H_A (x) 1 + 1 (x) H_B with H_A on the sharded (high) qubits: E0 = E0(A) + E0(B)
+    nA = wl + 3
+    xa, za, ca, _ = synth_pauli_sum(nA, 24, SEED + 9)
+    xbm, zbm, cb, _ = synth_pauli_sum(n - nA, 24, SEED + 10)
+    xs = np.concatenate([xa << np.uint64(n - nA), xbm])
+    zs = np.concatenate([za << np.uint64(n - nA), zbm])
+    cs = np.concatenate([ca, cb])
+    be.set_hamiltonian(xs, zs, cs)
+    e0, it, res = be.lanczos_ground(tol=1e-12, max_iter=600, seed=3)
+    if rank == 0:
+        from scipy.sparse.linalg import LinearOperator, eigsh
+
+        def e0_of(nq, x, z, c):
+            op = LinearOperator((1 << nq, 1 << nq), matvec=lambda v: co.apply(nq, x, z, c, v.astype(np.complex128)), dtype=np.complex128)
+            return float(eigsh(op, k=1, which="SA", tol=1e-13, return_eigenvectors=False)[0])
+        ea, eb = e0_of(nA, xa, za, ca), e0_of(n - nA, xbm, zbm, cb)
+        out["lanczos_rel_err"] = abs(e0 - (ea + eb)) / abs(ea + eb)
+        out["lanczos_iterations"] = int(it)
+    be.close()
+    return out
 
 
 def run_gpu(args):
@@ -198,8 +292,8 @@ def run_gpu(args):
     n = args.qubits + wl
     n_terms = args.terms
     xm, zm, cf, c_plain = synth_pauli_sum(n, n_terms, SEED)
-    T = len(xm)
     N = 1 << n
+    failures = []
 
     be = xb.Backend(n, device=local_rank, rank=rank, world=world, comm_id=comm_id)
     be.set_option("expect-engine", args.engine)
@@ -210,29 +304,11 @@ def run_gpu(args):
     be.set_option("tile-planner", args.planner)
     be.set_option("tile-dispatch", args.dispatch)
     be.set_option("expect-kernel", args.expect_kernel)
+    t0 = time.perf_counter()
     be.set_hamiltonian(xm, zm, cf)
+    set_ham_ms = (time.perf_counter() - t0) * 1e3
     Tn, G = be.hamiltonian_stats()
-
-    # correctness guard (untimed): a seeded product state has an exact, vector-free answer
-    rng = np.random.default_rng(SEED + 1)
-    a, b = rng.uniform(0, np.pi, n), rng.uniform(0, 2 * np.pi, n)
-    be.product_state(a, b)
-    e_prod = be.expectation().real
-    want = float(np.dot(c_plain, product_state_expectations(xm, zm, a, b)))
-    check_rel = abs(e_prod - want) / max(1.0, float(np.abs(c_plain).sum()))
-
-    be.random_state(0, SEED)        # input resident in HBM; 2^28 * 16 B = 4.3 GB >> 126 MB L2
-    apply_op = args.op == "apply"
-    if apply_op:
-        be.n_slots(2)
-
-    def step():
-        if apply_op:
-            be.apply_h(0, 1, want_alpha=False)      # dst = H psi (one Lanczos matrix-vector product)
-            return 0j
-        if args.op == "terms":
-            return be.expectation(per_term=True)[0]     # energy + per-term <P_k> (the reference's per-kernel exp-val-z)
-        return be.expectation()
+    plan = be.plan_stats()
 
     def barrier():
         if world > 1:
@@ -240,16 +316,70 @@ def run_gpu(args):
             dist.barrier()
         be.synchronize()
 
+    # ---- correctness guards (untimed; a failure makes the run exit 1) ----
+    # (i) a seeded product state has an exact, vector-free answer: sum_k c_k prod_q <sigma_q>
+    rng = np.random.default_rng(SEED + 1)
+    a, b = rng.uniform(0, np.pi, n), rng.uniform(0, 2 * np.pi, n)
+    be.product_state(a, b)
+    e_prod = be.expectation().real
+    want = float(np.dot(c_plain, product_state_expectations(xm, zm, a, b)))
+    check = {"product_state_rel_err": abs(e_prod - want) / abs(want), "product_state_energy": [e_prod, want]}
+    if not check["product_state_rel_err"] <= GUARD_TOL:
+        failures.append(f"product-state <psi|H|psi> off by {check['product_state_rel_err']:.3e} relative")
+    # (ii) N = 1: a host-generated normalised complex Gaussian against the CPU oracle on the bounded term sample (SURVEY.md 8d config 4 ii);
+    #      the oracle run is also the timed CPU baseline
+    cpu_base = None
+    if world == 1 and not args.no_cpu:
+        co = load_oracle()
+        cpu_base, _, k_cpu, e_cpu = cpu_baseline(co, n, xm, zm, cf, args.cpu_terms)
+        be.set_hamiltonian(xm[:k_cpu], zm[:k_cpu], cf[:k_cpu])
+        be.upload(host_random_state(n))
+        e_gpu = be.expectation()
+        check["random_state_vs_oracle_rel_err"] = abs(e_gpu - e_cpu) / abs(e_cpu)
+        check["random_state_vs_oracle_terms"] = int(k_cpu)
+        check["random_state_energy"] = [e_gpu.real, e_cpu.real]
+        if not check["random_state_vs_oracle_rel_err"] <= GUARD_TOL:
+            failures.append(f"random-state <psi|H|psi> differs from the oracle by {check['random_state_vs_oracle_rel_err']:.3e} relative")
+        _CPU_PSI.clear()
+        be.set_hamiltonian(xm, zm, cf)
+    # (iii) N >= 2: sharded H psi / <psi|H|psi> / Lanczos of a small register against the oracle
+    if world > 1 and not args.no_shard_check:
+        sc = sharded_parity_check(xb, dist, torch, rank, world, local_rank)
+        check["sharded"] = sc
+        if rank == 0:
+            if not sc["expect_err_over_sum_abs_c"] <= 1e-12:
+                failures.append(f"sharded <psi|H|psi> off by {sc['expect_err_over_sum_abs_c']:.3e} (sum |c|)")
+            if not sc["lanczos_rel_err"] <= GUARD_TOL:
+                failures.append(f"sharded Lanczos E0 off by {sc['lanczos_rel_err']:.3e} relative")
+        if not sc["apply_max_err_over_sum_abs_c"] <= 1e-12:
+            failures.append(f"sharded H psi off by {sc['apply_max_err_over_sum_abs_c']:.3e} (sum |c|)")
+
+    # ---- the timed region: K steps of <psi|H|psi> with the state resident in HBM (2^28 * 16 B = 4.3 GB per GPU >> 126 MB L2) ----
+    be.random_state(0, SEED)
+    op = args.op
+
+    def step():
+        if op == "apply":
+            be.apply_h(0, 1, want_alpha=False)      # dst = H psi (one Lanczos matrix-vector product)
+            return 0j
+        if op == "terms":
+            return be.expectation(per_term=True)[0]     # energy + per-term <P_k> (the reference's per-kernel exp-val-z)
+        return be.expectation()
+
+    if op == "apply":
+        be.n_slots(2)
     for _ in range(args.warmup):
         step()
     barrier()
     l0 = be.kernel_launches()
-    kernel_ms = []
+    kernel_ms, xch = [], []
     with ClockSampler(local_rank) as clk:
         be.timer_start()
         for _ in range(args.steps):
             e = step()
             kernel_ms.append(be.last_kernel_ms())
+            if world > 1 and op == "expect":
+                xch.append(be.last_exchange())
         ms = be.timer_stop()
         barrier()
     launches = be.kernel_launches() - l0
@@ -259,123 +389,198 @@ def run_gpu(args):
         ms = float(t.item())
     ms_per_step = ms / args.steps
     value = Tn * N / (ms_per_step * 1e-3)
+    clocks = clk.summary()
 
-    # end to end through the C ABI with host buffers: tables + state from pinned host memory, energy back
-    e2e = None
-    if world == 1:
-        host = torch.empty(be.n_local * 2, dtype=torch.float64).pin_memory()
-        host_np = host.numpy().view(np.complex128)
-        be.download(0, out=host_np)
+    # ---- end to end through the C ABI with host buffers: state from pinned host memory, energy back to the host ----
+    # The Hamiltonian tables stay resident, as the reference builds its per-term kernels once per VQE run (VQEProgram::build) and
+    # then calls execute() per parameter vector; set_hamiltonian (host planning + table upload) is reported separately.
+    host = torch.empty(be.n_local * 2, dtype=torch.float64).pin_memory()
+    host_np = host.numpy().view(np.complex128)
+    be.download(0, out=host_np)
+    be.upload(host_np)
+    step()
+    barrier()
+    reps = max(1, min(args.steps, 2))
+    t0 = time.perf_counter()
+    for _ in range(reps):
         be.upload(host_np)
         step()
-        be.synchronize()
-        t0 = time.perf_counter()
-        reps = max(1, min(args.steps, 2))
-        for _ in range(reps):
-            be.set_hamiltonian(xm, zm, cf)
-            be.upload(host_np)
-            e2 = step()
-            if apply_op:
-                be.download(1, out=host_np)
-        be.synchronize()
-        dt = (time.perf_counter() - t0) / reps
-        e2e = {"value": Tn * N / dt, "unit": UNIT, "h2d_bytes_per_step": int(be.n_local * 16 + T * 32),
-               "d2h_bytes_per_step": int(be.n_local * 16) if apply_op else 16, "ms_per_step": dt * 1e3}
-        del host
-    else:
-        host = torch.empty(be.n_local * 2, dtype=torch.float64).pin_memory()
-        host_np = host.numpy().view(np.complex128)
-        be.download(0, out=host_np)
-        barrier()
-        t0 = time.perf_counter()
-        be.set_hamiltonian(xm, zm, cf)
-        be.upload(host_np)
-        step()
-        if apply_op:
+        if op == "apply":
             be.download(1, out=host_np)
-        barrier()
-        dt = time.perf_counter() - t0
+    barrier()
+    dt = (time.perf_counter() - t0) / reps
+    if world > 1:
         tt = torch.tensor([dt], dtype=torch.float64, device="cuda")
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dt = float(tt.item())
-        e2e = {"value": Tn * N / dt, "unit": UNIT, "h2d_bytes_per_step": int(be.n_local * 16 + T * 32),
-               "d2h_bytes_per_step": int(be.n_local * 16) if apply_op else 16, "ms_per_step": dt * 1e3}
+    e2e = {"value": Tn * N / dt, "unit": UNIT, "h2d_bytes_per_step": int(be.n_local * 16),
+           "d2h_bytes_per_step": int(be.n_local * 16) if op == "apply" else 16, "ms_per_step": dt * 1e3,
+           "includes": "per step: state H2D from pinned host memory + the op + result D2H; the Hamiltonian tables are resident "
+                       "(set once per VQE run, as the reference's VQEProgram::build)",
+           "set_hamiltonian_ms": set_ham_ms,
+           "value_with_set_hamiltonian_every_step": Tn * N / (dt + set_ham_ms * 1e-3)}
+    del host
 
+    # ---- extra: H psi and one Lanczos step on the same operator (N = 1; the headline stays <psi|H|psi>) ----
+    extra = {}
+    if world == 1 and op == "expect" and not args.no_extra:
+        be.n_slots(3)
+        be.random_state(0, SEED)
+        be.apply_h(0, 1, want_alpha=False)             # plans H psi, warms up
+        be.synchronize()
+        la = be.kernel_launches()
+        t_ms = []
+        for _ in range(2):
+            be.apply_h(0, 1, want_alpha=False)
+            t_ms.append(be.last_kernel_ms())
+        la = (be.kernel_launches() - la) // 2
+        a_ms = float(np.mean(t_ms))
+        nb_a = be.plan_stats()["apply_batches"]
+        peak, _ = measured_peak_gbs()
+        alg = 16.0 * be.n_local * (G + 1)
+        model = 16.0 * be.n_local * (3 * nb_a - 1)     # per batch: src read + dst read-modify-write (the first batch only writes)
+        extra["apply"] = {"op": "dst = H psi (b200vqe_apply_h), same operator", "ms": a_ms, "value": Tn * N / (a_ms * 1e-3), "unit": UNIT,
+                          "launches": int(la), "n_batches": int(nb_a),
+                          "roofline": {"bound": "hbm", "achieved": alg / (a_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                                       "frac": alg / (a_ms * 1e-3) / 1e9 / peak,
+                                       "note": "ALGORITHMIC bytes 16 B x 2^n x (G + 1) (SURVEY.md 8d) / CUDA-event time",
+                                       "dram_model": {"bytes": model, "achieved": model / (a_ms * 1e-3) / 1e9, "frac": model / (a_ms * 1e-3) / 1e9 / peak,
+                                                      "note": "16 B x 2^n x (3 n_batches - 1): src read + dst read + dst write per batch of xmask groups"}}}
+        # one Lanczos iteration = H psi (alpha fused or one k_alpha pass) + k_lanczos_update; measured as the slope of two short runs
+        m1, m2 = 3, 9
+
+        def lanczos_steps(m):
+            try:
+                be.lanczos_ground(tol=1e-300, max_iter=m, seed=5)
+            except xb.B200Error as ex:
+                if ex.code != -6:          # B200VQE_ENOCONV: the run is meant to stop at max_iter
+                    raise
+            be.synchronize()
+
+        t0 = time.perf_counter()
+        lanczos_steps(m1)
+        d1 = time.perf_counter() - t0
+        l1 = be.kernel_launches()
+        t0 = time.perf_counter()
+        lanczos_steps(m2)
+        d2 = time.perf_counter() - t0
+        l2 = be.kernel_launches() - l1
+        it_ms = (d2 - d1) / (m2 - m1) * 1e3
+        alg_l = alg + 80.0 * be.n_local
+        extra["lanczos_step"] = {"op": "one Lanczos iteration: H psi + alpha + three-term update with fused norm", "ms": it_ms,
+                                 "value": Tn * N / (it_ms * 1e-3), "unit": UNIT, "launches_per_iteration": int(round(l2 / m2)),
+                                 "roofline": {"bound": "hbm", "achieved": alg_l / (it_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                                              "frac": alg_l / (it_ms * 1e-3) / 1e9 / peak,
+                                              "note": "ALGORITHMIC bytes of H psi + 5 x 16 B x 2^n for the fused vector update / host-timed slope of two runs"}}
+        be.n_slots(1)
+
+    if world > 1:
+        ok = torch.tensor([0 if failures else 1], dtype=torch.int32, device="cuda")
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()) == 0 and not failures:
+            failures.append("a correctness guard failed on another rank")
     if rank != 0:
         if world > 1:
             dist.barrier()
             dist.destroy_process_group()
+        if failures:
+            sys.exit(1)
         return
 
     peak, peak_src = measured_peak_gbs()
+    apply_op = op == "apply"
     # algorithmic bytes of one <psi|H|psi> on one GPU: 16 B x local amplitudes x groups
     alg_bytes = 16.0 * be.n_local * (G + 1 if apply_op else G)
-    k_ms = ms_per_step if args.op == "terms" else float(np.mean(kernel_ms))     # terms: energy launch + per-term launch
+    k_ms = ms_per_step if op == "terms" else float(np.mean(kernel_ms))     # terms: energy launch + per-term launch
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
-    traffic = traffic_tile = None
-    tpath = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tpath):
-        try:
-            tj = json.load(open(tpath))
-            traffic = tj.get("k_expect_energy_bytes_per_step")
-            # ncu --set full capture of k_tile_expect on this exact workload (dram__bytes_read.sum + dram__bytes_write.sum, one launch)
-            if tj.get("k_tile_expect", {}).get("n_qubits") == n and tj["k_tile_expect"].get("n_terms") == int(Tn):
-                traffic_tile = tj["k_tile_expect"]["dram_bytes_per_launch"]
-        except Exception:
-            traffic = None
     tile = args.engine != "stream"
-    if tile and traffic_tile is not None:
-        traffic = traffic_tile
+    kernel_name = (("k_tile_apply" if tile else "k_apply<8,true>") if apply_op else
+                   (("k_tile_expect_db<3>" if args.tile_bits == 11 else
+                     {"auto": "k_tile_expect_pipe", "pipe": "k_tile_expect_pipe", "ring": "k_tile_expect_ring",
+                      "classic": "k_tile_expect<2,false,%d>" % args.dispatch}[args.expect_kernel])
+                    if tile else "k_expect_energy<8,true>"))
+    # DRAM traffic of the step: the tile engine streams this rank's amplitudes once per batch (pair registers: the peer slab too),
+    # modelled from the LIVE plan; the ncu capture of the same launch (profiles/traffic.json) is quoted when it matches the plan
+    traffic = traffic_src = None
+    if tile and op == "expect":
+        passes = plan["expect_batches"]
+        traffic = 16.0 * be.n_local * passes
+        traffic_src = f"model: 16 B x 2^{int(np.log2(be.n_local))} amplitudes x {passes} batches of the live plan (b200vqe_plan_stats)"
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["k_tile_expect_pipe"]
+            if tj.get("n_qubits") == n and tj.get("n_terms") == int(Tn) and tj.get("n_batches") == passes and world == 1:
+                traffic = float(tj["dram_bytes_per_launch"])
+                traffic_src = "ncu dram__bytes_read.sum + dram__bytes_write.sum of this launch (profiles/traffic.json: " + tj.get("how", "") + ")"
+        except Exception:
+            pass
     roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-            "kernel": ("k_tile_apply" if tile else "k_apply<8,true>") if apply_op else (("k_tile_expect_db<3>" if args.tile_bits == 11 else "k_tile_expect<2>") if tile else "k_expect_energy<8,true>"),
-            "peak_source": peak_src,
+            "traffic_source": traffic_src, "kernel": kernel_name, "peak_source": peak_src,
             "launches_per_step": int(launches // max(1, args.steps)),
             "note": ("achieved = ALGORITHMIC bytes 16 B x 2^n_local x (G + 1) (SURVEY.md 8d: G partner reads + one write) / CUDA-event "
-                     "time of the step's H.psi launch(es); the tile engine reads src once and read-modify-writes dst once per "
+                     "time of the step's H.psi launches; the tile engine reads src once and read-modify-writes dst once per "
                      "BATCH of xmask groups (48 B per amplitude per batch), so frac > 1 is expected") if apply_op else
-                    ("achieved = ALGORITHMIC bytes 16 B x 2^n_local x G (SURVEY.md 8d) / CUDA-event time of the step's single "
-                     "k_tile_expect launch. The tile engine evaluates >= 9 xmask groups per HBM read of the state (GF(2)-subspace "
-                     "tiles in shared memory), so its DRAM traffic is ~16 B x 2^n x n_batches and frac > 1 is expected; the "
-                     "kernel is bound by shared-memory bandwidth (see 'shared_memory' and DESIGN.md 3.1)") if tile else
+                    ("achieved = ALGORITHMIC bytes 16 B x 2^n_local x G (SURVEY.md 8d) / CUDA-event time of the step's <psi|H|psi> launch(es). "
+                     "The tile engine evaluates ~14 xmask groups per HBM read of the state (GF(2)-subspace tiles in shared memory), so frac > 1 "
+                     "by design; the physical bounds of the kernel are in 'dram' (bytes it really moves) and 'lsu' (shared-memory pipe)") if tile else
                     ("achieved = 16 B x 2^n_local x G per step / CUDA-event time of the step's k_expect_energy launches "
                      "(one launch per xmask bucket); the pair form reads each pair once, so DRAM traffic is about half the model")}
-    clocks = clk.summary()
-    if tile and not apply_op and args.op == "expect" and traffic:
-        # the two physical bounds of the tile kernel next to the algorithmic one: measured DRAM bytes of this launch and the
-        # shared-memory bytes its design cannot avoid (16 B partner read per pair per group, 17/16 for the all-registers class,
-        # plus the tile fill of every batch) against 128 B/clk/SM at the SM clock sampled during the run
-        n_batches = traffic / (16.0 * be.n_local)
-        smem_bytes = 16.0 * (G * (be.n_local / 2) * (17.0 / 16.0) + n_batches * be.n_local)
-        smem_peak = torch.cuda.get_device_properties(local_rank).multi_processor_count * 128.0 * float(clocks.get("sm_mhz") or 0) * 1e6 / 1e9
-        roof["dram"] = {"achieved": traffic / (k_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "frac": traffic / (k_ms * 1e-3) / 1e9 / peak}
-        if smem_peak > 0:
-            roof["shared_memory"] = {"achieved": smem_bytes / (k_ms * 1e-3) / 1e9, "peak": smem_peak, "unit": "GB/s",
-                                     "frac": smem_bytes / (k_ms * 1e-3) / 1e9 / smem_peak,
-                                     "note": "design floor of shared-memory bytes / (SMs x 128 B/clk x sampled SM clock)"}
+    if tile and op == "expect" and traffic:
+        n_sm = torch.cuda.get_device_properties(local_rank).multi_processor_count
+        roof["dram"] = {"achieved": traffic / (k_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "frac": traffic / (k_ms * 1e-3) / 1e9 / peak,
+                        "n_batches": plan["expect_batches"]}
+        clk_hz = float(clocks.get("sm_mhz") or 0) * 1e6
+        if clk_hz > 0:
+            # LSU data-pipe wavefronts the design cannot avoid (one 128-byte wavefront per clock per SM): per tile the cp.async fill
+            # (8 per LDGSTS warp-instruction, 128 of them) and the own-amplitude reads (128 LDS.128 x 4), per generic record 64 LDS.128 x 4
+            tiles = be.n_local / 4096.0 * plan["expect_batches"]
+            wave = tiles * (128 * 8 + 128 * 4) + 0.72 * G * (be.n_local / 4096.0) * 64 * 4
+            roof["lsu"] = {"achieved": wave / (k_ms * 1e-3) / 1e9, "peak": n_sm * clk_hz / 1e9, "unit": "G wavefronts/s",
+                           "frac": wave / (k_ms * 1e-3) / (n_sm * clk_hz),
+                           "note": "design floor of shared-memory/LDGSTS wavefronts (~28 % of the records are pure-register: no partner read) / (SMs x sampled SM clock); "
+                                   "ncu l1tex__data_pipe_lsu_wavefronts: profiles/r2_ncu_full_k_tile_expect_pipe_400terms.txt"}
+    if world > 1 and xch:
+        x_ms = float(np.mean([v[0] for v in xch]))
+        x_by = float(np.mean([v[1] for v in xch]))
+        gbs = x_by / (x_ms * 1e-3) / 1e9 if x_ms > 0 else None
+        roof["nvlink"] = {"bytes_per_gpu_per_step": x_by, "exchange_ms_per_step": x_ms, "achieved": gbs,
+                          "peak": NVLINK_NOMINAL_GBS, "unit": "GB/s", "frac": gbs / NVLINK_NOMINAL_GBS if gbs else None,
+                          "frac_of_measured_770": gbs / NVLINK_MEASURED_GBS if gbs else None,
+                          "exchange_share_of_step": x_ms / k_ms if k_ms > 0 else None,
+                          "note": "slab swaps of the x_rank classes (grouped ncclSend/ncclRecv, both directions at once): bytes this rank RECEIVES per step / "
+                                  "CUDA-event time of the swaps on the communication stream, summed over the classes; the swaps run concurrently with the "
+                                  "tile kernels of the previous class, so exchange_share_of_step is overlapped time, not added time"}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": {"workload": f"synthetic {n}-qubit random Pauli sum, {Tn} terms, fp64 " + ("H.psi" if apply_op else ("<psi|H|psi> + per-term <P_k>" if args.op == "terms" else "<psi|H|psi>")),
+            "config": {"workload": f"synthetic {n}-qubit random Pauli sum, {Tn} terms, fp64 " + ("H.psi" if apply_op else ("<psi|H|psi> + per-term <P_k>" if op == "terms" else "<psi|H|psi>")),
                        "n_qubits": n, "n_terms": int(Tn), "n_xmask_groups": int(G), "amplitudes_per_gpu": int(be.n_local),
-                       "parallelism": f"state sharded over {world} GPU(s) by high index bits",
+                       "parallelism": f"state sharded over {world} GPU(s) by high index bits" + (
+                           "; per x_rank class the two ranks of a pair swap slabs (ncclSend/ncclRecv) and evaluate half of the pair register each, "
+                           "one ncclAllReduce of the partials" if world > 1 else ""),
                        "l2": "inputs larger than L2 (4.3 GB state per GPU vs 126 MB)"},
-            "roofline": roof, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
-            "check": {"product_state_rel_err": check_rel, "energy": [e.real, e.imag]}}
-    if world == 1 and not args.no_cpu:
-        base, _, _ = cpu_baseline(n, xm, zm, cf, args.cpu_terms)
-        line["cpu_baseline"] = base
+            "roofline": roof, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "check": check, "plan": plan}
+    line["check"]["energy"] = [e.real, e.imag]
+    if extra:
+        line["extra"] = extra
+    if cpu_base is not None:
+        line["cpu_baseline"] = cpu_base
+    if failures:
+        line["failed"] = failures
     emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    if failures:
+        print("bench.py: correctness guard failed: " + "; ".join(failures), file=sys.stderr)
+        sys.exit(1)
 
 
 _REAL_STDOUT = None
 
 
 def _guard_stdout():
-    """stdout carries exactly ONE JSON line: everything libraries print (NCCL's version banner, torch warnings) goes to
-    stderr; emit() writes the line to the saved descriptor."""
+    """stdout carries exactly ONE JSON line: everything libraries print (NCCL's version banner and INFO lines, torch warnings)
+    goes to stderr; emit() writes the line to the saved descriptor."""
     global _REAL_STDOUT
     sys.stdout.flush()
     _REAL_STDOUT = os.dup(1)
@@ -401,7 +606,9 @@ def main():
     ap.add_argument("--qubits", type=int, default=N_QUBITS_1GPU, help="qubits per GPU shard (default: the named config)")
     ap.add_argument("--terms", type=int, default=N_TERMS)
     ap.add_argument("--cpu-terms", type=int, default=256, help="terms in the bounded CPU-baseline sample")
-    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU oracle legs (cpu_baseline and the random-state cross-check)")
+    ap.add_argument("--no-extra", action="store_true", help="skip the H psi / Lanczos-step measurements")
+    ap.add_argument("--no-shard-check", action="store_true", help="N > 1: skip the small sharded parity check")
     ap.add_argument("--op", default="expect", choices=["expect", "apply", "terms"], help="expect: <psi|H|psi> (headline); apply: dst = H psi; terms: <psi|H|psi> plus every <P_k>")
     ap.add_argument("--engine", default="auto", choices=["auto", "tile", "stream"], help="<psi|H|psi> kernel family")
     ap.add_argument("--tile-ctas", type=int, default=2, choices=[2, 3], help="tile engine: resident CTAs per SM")

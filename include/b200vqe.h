@@ -118,6 +118,14 @@ int b200vqe_local_amplitudes(b200vqe_handle h, uint64_t *count, uint64_t *first_
 int b200vqe_set_hamiltonian(b200vqe_handle h, int64_t n_terms, const uint64_t *xmask,
                             const uint64_t *zmask, const double *coef_re, const double *coef_im);
 int b200vqe_hamiltonian_stats(b200vqe_handle h, int64_t *n_terms, int64_t *n_groups);
+/* Tile-engine plan of the handle's Hamiltonian: out[0] batches (= HBM passes over this rank's amplitudes) of <psi|H|psi>,
+ * out[1] xmask groups, out[2] batches of H psi (0 until the first H psi plans them), out[3] x_rank classes of a sharded
+ * <psi|H|psi>, out[4] chunk bits, out[5] tile bits. */
+int b200vqe_plan_stats(b200vqe_handle h, int64_t out[6]);
+/* NVLink exchange of the last sharded b200vqe_expectation: CUDA-event time [ms] of the slab swaps on the communication stream
+ * (summed) and the bytes this rank received.  The counterpart of the reference's only collective is the final all-reduce
+ * (task/tasks/ComputeEnergyVQETask.cpp:114-126). */
+int b200vqe_last_exchange(b200vqe_handle h, double *ms, double *bytes);
 
 /* Host-only view of the tile-engine plan (see csrc/tile_plan.hpp) for a Hermitian term list, exactly as
  * b200vqe_set_hamiltonian builds it for <psi|H|psi> (batch capacities included): raw TileBatch[160 B],
@@ -140,6 +148,13 @@ int b200vqe_debug_apply_plan(int n_qubits, int rank, int world, int chunk_bits, 
                              const uint64_t *zmask, const double *coef_re, const double *coef_im, int64_t *n_batches,
                              int64_t *n_records, int64_t *n_plan_terms, int64_t *n_classes, void *batches, void *records,
                              void *terms, int32_t *classes);
+
+/* Host-only: the <psi|H|psi> plans of shard `rank` of `world` >= 2: one per x_rank class, built over the pair register {own slab,
+ * slab of rank ^ x_rank} (class 0: the own slab); classes[4k..4k+3] = x_rank, qubits of that register, first batch, end batch. */
+int b200vqe_debug_expect_class_plan(int n_qubits, int rank, int world, int chunk_bits, int64_t n_terms, const uint64_t *xmask,
+                                    const uint64_t *zmask, const double *coef_re, const double *coef_im, int64_t *n_batches,
+                                    int64_t *n_records, int64_t *n_plan_terms, int64_t *n_classes, void *batches, void *records,
+                                    void *terms, int32_t *classes);
 
 /* Host-only: slab and tile-engine share of `rank` in a register sharded over `world` ranks (what
  * b200vqe_create_sharded / b200vqe_expectation use).  No device needed. */

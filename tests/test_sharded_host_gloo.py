@@ -50,6 +50,13 @@ def _worker(rank, world, port, n, T, seed, q):
     part = tp.replay(n, 3, B, G, Tt, psi, tile_begin=tb, tile_count=tc)
     tot = torch.tensor([part], dtype=torch.float64)
     dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    # the capacity-scaling decomposition b200vqe_expectation uses on a sharded handle: per x_rank class the pair register
+    # {own slab, slab of rank ^ x_rank}, half of its tiles per rank; partials all-reduced
+    tp.replay_expect_classes.ham = (xm, zm, cf)
+    part_c = tp.replay_expect_classes(n, 3, psi, rank, world)
+    tot_c = torch.tensor([part_c], dtype=torch.float64)
+    dist.all_reduce(tot_c, op=dist.ReduceOp.SUM)
+    assert abs(tot_c.item() - tot.item()) < 1e-11 * float(np.abs(cf).sum())
     # the same with the 2048-amplitude tiles / per-key records of the double-buffered kernel
     _, _, tb11, tc11 = _layout(lib, n, rank, world, tile_bits=11)
     B11, _, T11 = tp.get_plan(n, 3, xm, zm, cf, tb=11)

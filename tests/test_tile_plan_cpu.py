@@ -229,6 +229,53 @@ def replay_apply(n, c, B, R, T, classes, psi, rank=0, world=1):
     return out
 
 
+def get_expect_class_plan(n, c, xm, zm, cf, rank, world):
+    """b200vqe_debug_expect_class_plan: the <psi|H|psi> tables of one shard (one plan per x_rank class over the pair register)."""
+    lib = xb.capi.lib()
+    xm = np.ascontiguousarray(xm, np.uint64)
+    zm = np.ascontiguousarray(zm, np.uint64)
+    cr, ci = np.ascontiguousarray(cf.real), np.ascontiguousarray(cf.imag)
+    nb, nr, nt, nc = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int64()
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)
+    args = (C.c_int(n), C.c_int(rank), C.c_int(world), C.c_int(c), C.c_int64(len(xm)), vp(xm), vp(zm), vp(cr), vp(ci),
+            C.byref(nb), C.byref(nr), C.byref(nt), C.byref(nc))
+    assert lib.b200vqe_debug_expect_class_plan(*args, None, None, None, None) == 0
+    B, R, T = np.zeros(nb.value, BATCH_DT), np.zeros(nr.value, REC_DT), np.zeros(nt.value, TERM_DT)
+    cls = np.zeros(4 * nc.value, np.int32)
+    assert lib.b200vqe_debug_expect_class_plan(*args, vp(B), vp(R), vp(T), vp(cls)) == 0
+    return B, R, T, cls.reshape(-1, 4)
+
+
+def replay_expect_classes(n, c, psi, rank, world):
+    """What b200vqe_expectation evaluates on shard `rank`: class 0 on the own slab, class x_rank on HALF of the tiles of the pair
+    register {slab of the lower rank, slab of the higher rank} of the pair (rank, rank ^ x_rank); the lower rank takes the lower
+    half of the tiles.  Returns this rank's partial."""
+    nl = n - int(np.log2(world))
+    nloc = 1 << nl
+    own = psi[rank * nloc:(rank + 1) * nloc]
+    xm, zm, cf = replay_expect_classes.ham
+    B, R, T, classes = get_expect_class_plan(n, c, xm, zm, cf, rank, world)
+    total, seen = 0.0, []
+    for x_rank, n_reg, b0, b1 in classes:
+        x_rank, n_reg = int(x_rank), int(n_reg)
+        seen.append(x_rank)
+        if x_rank == 0:
+            assert n_reg == nl
+            total += replay_records(nl, c, B[b0:b1], R, T, own)
+        else:
+            assert n_reg == nl + 1
+            peer = rank ^ x_rank
+            lo_r, hi_r = min(rank, peer), max(rank, peer)          # the same pair register on both ranks of the pair
+            reg = np.concatenate([psi[lo_r * nloc:(lo_r + 1) * nloc], psi[hi_r * nloc:(hi_r + 1) * nloc]])
+            tiles = 1 << (n_reg - TILE_BITS)
+            per = tiles // 2
+            role = 0 if rank < peer else 1
+            tb, tc = (per * role, per) if per else (0, tiles if role == 0 else 0)
+            total += replay_records(n_reg, c, B[b0:b1], R, T, reg, tile_begin=tb, tile_count=tc)
+    assert seen == sorted(seen)
+    return total
+
+
 def random_hamiltonian(n, T, seed, weights=None):
     rng = np.random.default_rng(seed)
     pa = rng.integers(0, 4, size=(T, n)) if weights is None else rng.choice(4, size=(T, n), p=weights)
@@ -308,6 +355,21 @@ def test_apply_plan_replay_matches_oracle(n, T, c, seed, world, weights):
         assert len(Tt) == len(xm) and sorted(set(classes[:, 0])) == list(classes[:, 0])
         got = replay_apply(n, c, B, R, Tt, classes, psi, rank, world)
         assert np.abs(got - want[rank * nloc:(rank + 1) * nloc]).max() < 1e-12 * np.abs(cf).sum()
+
+
+@pytest.mark.parametrize("n,T,c,seed,world", [(14, 60, 3, 31, 2), (15, 80, 3, 32, 4), (16, 120, 3, 33, 8), (15, 50, 2, 34, 4)])
+def test_sharded_expectation_class_plans_replay_matches_oracle(n, T, c, seed, world):
+    """Host logic of the capacity-scaling sharded <psi|H|psi> on the CPU: every rank's class plans replayed in numpy over {own slab,
+    one peer slab} -- never the whole register -- and summed over the ranks (the device all-reduces them) give the oracle's energy."""
+    xm, zm, cf = random_hamiltonian(n, T, seed)
+    rng = np.random.default_rng(seed + 50)
+    psi = rng.normal(size=1 << n) + 1j * rng.normal(size=1 << n)
+    psi /= np.linalg.norm(psi)
+    eo, _ = co.expect(n, xm, zm, cf, psi)
+    replay_expect_classes.ham = (xm, zm, cf)
+    parts = [replay_expect_classes(n, c, psi, r, world) for r in range(world)]
+    assert abs(sum(parts) - eo.real) < 1e-11 * np.abs(cf).sum()
+    assert sum(abs(p) > 0 for p in parts) == world
 
 
 def test_batch_capacity_splits_large_groups_and_batches():

@@ -254,6 +254,19 @@ class Backend:
         self._ck(lib().b200vqe_hamiltonian_stats(self.h, C.byref(t), C.byref(g)))
         return t.value, g.value
 
+    def plan_stats(self):
+        """Tile-engine plan: batches (= HBM passes over this rank's amplitudes) of <psi|H|psi>, xmask groups, batches of H psi
+        (0 until the first H psi), x_rank classes, chunk bits, tile bits."""
+        out = (C.c_int64 * 6)()
+        self._ck(lib().b200vqe_plan_stats(self.h, out))
+        return dict(zip(("expect_batches", "groups", "apply_batches", "expect_classes", "chunk_bits", "tile_bits"), [int(v) for v in out]))
+
+    def last_exchange(self):
+        """(ms, bytes received by this rank) of the NVLink slab swaps of the last sharded <psi|H|psi>."""
+        ms, by = C.c_double(), C.c_double()
+        self._ck(lib().b200vqe_last_exchange(self.h, C.byref(ms), C.byref(by)))
+        return ms.value, by.value
+
     def reset(self, slot: int = 0, basis_index: int = 0):
         self._ck(lib().b200vqe_state_reset(self.h, C.c_int(slot), C.c_uint64(basis_index)))
 

@@ -264,6 +264,7 @@ static int create_common(int n_qubits, int device, int rank, int world, const ch
         cudaEventCreateWithFlags(&h->ev_src_ready, cudaEventDisableTiming);
         cudaEventCreateWithFlags(&h->ev_gathered, cudaEventDisableTiming);
         for (int i = 0; i < 2; ++i) { cudaEventCreateWithFlags(&h->ev_recv[i], cudaEventDisableTiming); cudaEventCreateWithFlags(&h->ev_free[i], cudaEventDisableTiming); }
+        for (int i = 0; i < kMaxWorld; ++i) { cudaEventCreate(&h->ev_x0[i]); cudaEventCreate(&h->ev_x1[i]); }
         if (!g_nccl.load(g_err)) { delete h; return B200VQE_ECOMM; }
         ncclUniqueId u;
         memcpy(&u, id, 128);
@@ -287,7 +288,8 @@ int b200vqe_destroy(b200vqe_handle h) {
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
     if (h->comm_stream) { cudaStreamSynchronize(h->comm_stream); cudaStreamDestroy(h->comm_stream); cudaEventDestroy(h->ev_src_ready); cudaEventDestroy(h->ev_gathered);
-        for (int i = 0; i < 2; ++i) { cudaEventDestroy(h->ev_recv[i]); cudaEventDestroy(h->ev_free[i]); } }
+        for (int i = 0; i < 2; ++i) { cudaEventDestroy(h->ev_recv[i]); cudaEventDestroy(h->ev_free[i]); }
+        for (int i = 0; i < kMaxWorld; ++i) { cudaEventDestroy(h->ev_x0[i]); cudaEventDestroy(h->ev_x1[i]); } }
     for (auto p : h->slots) if (p) cudaFree(p);
     if (h->gather) cudaFree(h->gather);
     if (h->xbuf) cudaFree(h->xbuf);

@@ -42,6 +42,14 @@ struct DeviceHam {
     std::vector<int64_t> tl_term_idx;   // plan term -> caller index (per-term output of the tile engine)
     std::vector<double> tl_term_u;      // unweighted coefficient of the plan term: coef (even nY) | i*coef (odd nY)
     std::vector<double> tl_term_r;      // <P_k> = r_k * (signed pair sum): Re i^nY (even nY) | -Im i^nY (odd nY)
+    // ... on a sharded register the full-register plan above serves only the per-term output and is built on its first use
+    // (tl_src keeps the terms until then); <psi|H|psi> itself uses one plan per x_rank class (which peer slab the partners live
+    // in), built over the PAIR REGISTER {own slab, slab of rank ^ x_rank} of nl + 1 qubits (class 0: the own slab, nl qubits)
+    struct TlSrc { uint64_t x, z; double u; int ny; int64_t idx; };
+    std::vector<TlSrc> tl_src; bool tl_built = false, tl_wanted = false;
+    struct ExpectClass { int x_rank; int n_reg; int b_begin, b_end; };
+    std::vector<ExpectClass> tc_classes;
+    TileBatch *tc_batches = nullptr; TileRec *tc_recs = nullptr; TileTerm *tc_terms = nullptr; int n_tc_batches = 0;
     // tile engine for H psi: one plan per x_rank class (which peer slab the partners live in), concatenated
     struct ApplyClass { int x_rank; int b_begin, b_end; };
     struct ApplySrc { uint64_t x, z; double cre, cim; int ny; int64_t idx; };
@@ -59,6 +67,8 @@ struct DeviceHam {
     void free_device() {
         cudaFree(gd_e); cudaFree(tz_e); cudaFree(tu_e); cudaFree(gd_a); cudaFree(tz_a); cudaFree(tv_a);
         cudaFree(tl_batches); cudaFree(tl_recs); cudaFree(tl_terms);
+        cudaFree(tc_batches); cudaFree(tc_recs); cudaFree(tc_terms);
+        tc_batches = nullptr; tc_recs = nullptr; tc_terms = nullptr;
         cudaFree(ta_batches); cudaFree(ta_recs); cudaFree(ta_terms);
         cudaFree(sw_batch); cudaFree(sw_groups); cudaFree(sw_terms);
         sw_batch = nullptr; sw_groups = nullptr; sw_terms = nullptr;
@@ -92,6 +102,9 @@ struct b200vqe_ctx {
     std::string err;
     int64_t launches = 0;
     double last_ms = 0.0;
+    // NVLink exchange of the last sharded <psi|H|psi> / H psi: CUDA-event time of the transfers on the communication stream
+    // (summed over the exchanges of the call) and the bytes this rank received
+    cudaEvent_t ev_x0[b200vqe::kMaxWorld] = {}, ev_x1[b200vqe::kMaxWorld] = {}; int n_xev = 0; double last_comm_bytes = 0.0;
     // particle-number sector (b200vqe_set_number_sector); sector_ne < 0: none
     int sector_ne = -1; bool sector_unit = true; uint64_t sector_rows[40] = {0};
     // options (string keys as in the reference's xacc::setOption map)

@@ -294,7 +294,7 @@ __global__ void __launch_bounds__(kBlock, MINB)
 k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_bytes, const TileBatch *__restrict__ batches, int n_batches,
               unsigned long long tile_begin, unsigned long long tile_count, const TileRec *__restrict__ recs,
               const TileTerm *__restrict__ terms, double *partials, unsigned *counter, double *out,
-              double *term_partials = nullptr, int n_plan_terms = 0) {
+              double *term_partials = nullptr, int n_plan_terms = 0, const double2 *__restrict__ psi_hi = nullptr, unsigned sel_mask = 0) {
     extern __shared__ __align__(16) unsigned char tile_raw[];
     double2 *tile = reinterpret_cast<double2 *>(tile_raw);
     __shared__ TileBatch sb;
@@ -371,7 +371,9 @@ k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_byte
             const unsigned hi = base ^ ((r & 1) ? rb0 : 0u) ^ ((r & 2) ? rb1 : 0u) ^ ((r & 4) ? rb2 : 0u) ^ ((r & 8) ? rb3 : 0u);
             // register r holds the amplitude with low index bits lo ^ Lambda(r): still one 128-byte line per 8 lanes
             const unsigned lor = DISP == 3 ? lo_b : (lo_b ^ ((r & 1) ? lm0 : 0u) ^ ((r & 2) ? lm1 : 0u) ^ ((r & 4) ? lm2 : 0u) ^ ((r & 8) ? lm3 : 0u));
-            a[r] = __ldcs(reinterpret_cast<const double2 *>(psi_b + ((unsigned long long)hi * chunk_bytes + lor)));   // streamed once per batch
+            // pair register of a sharded register (sel_mask != 0): chunks with that high-index bit set live in the peer's slab
+            const char *slab = (hi & sel_mask) ? reinterpret_cast<const char *>(psi_hi) : psi_b;
+            a[r] = __ldcs(reinterpret_cast<const double2 *>(slab + ((unsigned long long)(hi & ~sel_mask) * chunk_bytes + lor)));   // streamed once per batch
         }
         __syncthreads();                        // readers of the previous tile are done
 #pragma unroll
@@ -382,9 +384,10 @@ k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_byte
             have_next = wn < total && wn / tile_count == (unsigned long long)b;
             if (have_next) {
                 rep_next = tile_rep(sb, (unsigned)(tile_begin + (wn - (unsigned long long)b * tile_count)));
-                const unsigned h0 = rep_next ^ pcA;
-                prefetch_l2(psi_lo + (unsigned long long)h0 * chunk_bytes);
-                prefetch_l2(psi_lo + (unsigned long long)(h0 ^ rb0) * chunk_bytes);
+                const unsigned h0 = rep_next ^ pcA, h1 = h0 ^ rb0;
+                const char *hi_lo = reinterpret_cast<const char *>(psi_hi + lo);
+                prefetch_l2(((h0 & sel_mask) ? hi_lo : psi_lo) + (unsigned long long)(h0 & ~sel_mask) * chunk_bytes);
+                prefetch_l2(((h1 & sel_mask) ? hi_lo : psi_lo) + (unsigned long long)(h1 & ~sel_mask) * chunk_bytes);
             }
         }
         if constexpr (DISP == 1) {

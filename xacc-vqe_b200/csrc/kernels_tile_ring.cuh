@@ -427,7 +427,8 @@ struct PipeFillBatch {               // what a fill needs of its batch (shared m
 constexpr int kPipeSmemBytes = kRingStages * kRingTileBytes + kRingGroups * (int)(sizeof(RingTables) + sizeof(PipeFillBatch)) + kRingStages * 8 + 32 * 8;
 
 __global__ void __launch_bounds__(kRingThreads, 1)
-k_tile_expect_pipe(const double2 *__restrict__ psi, int C, int M, const TileBatch *__restrict__ batches, int n_batches,
+k_tile_expect_pipe(const double2 *__restrict__ psi, const double2 *__restrict__ psi_hi, unsigned sel_mask, int C, int M,
+                   const TileBatch *__restrict__ batches, int n_batches,
                    unsigned long long tile_begin, unsigned long long tile_count, const TileRec *__restrict__ recs,
                    const TileTerm *__restrict__ terms, double *partials, unsigned *counter, double *out) {
     extern __shared__ __align__(128) unsigned char ring_raw[];
@@ -456,7 +457,10 @@ k_tile_expect_pipe(const double2 *__restrict__ psi, int C, int M, const TileBatc
     PipeFillBatch &fb = fbs[g];
     const unsigned recs_u = smem_u32(tb.recs), terms_u = smem_u32(tb.terms);
     const unsigned long long step = (unsigned long long)kRingGroups * gridDim.x;
+    // pair register of a sharded <psi|H|psi> (backend_ham.inc): chunks whose high index has bit sel_mask set live in the
+    // slab received from the peer rank (psi_hi), the others in this rank's own slab; sel_mask = 0: one register
     const char *psi_b = reinterpret_cast<const char *>(psi);
+    const char *psi_h = reinterpret_cast<const char *>(psi_hi);
     double acc = 0.0;
 
     // ---- fill side: this group streams items 1 - g, 3 - g, 5 - g, ... (stage = item % 3) ----
@@ -492,7 +496,8 @@ k_tile_expect_pipe(const double2 *__restrict__ psi, int C, int M, const TileBatc
         for (int r = 0; r < 16; ++r) {
             const unsigned hi = base ^ ((r & 1) ? rb0 : 0u) ^ ((r & 2) ? rb1 : 0u) ^ ((r & 4) ? rb2 : 0u) ^ ((r & 8) ? rb3 : 0u);
             const unsigned lor = lo_b ^ ((r & 1) ? lm0 : 0u) ^ ((r & 2) ? lm1 : 0u) ^ ((r & 4) ? lm2 : 0u) ^ ((r & 8) ? lm3 : 0u);
-            cp_async16_u(dst + ((unsigned)r << 12), psi_b + (((unsigned long long)hi << chunk_shift) + lor));
+            const char *slab = (hi & sel_mask) ? psi_h : psi_b;
+            cp_async16_u(dst + ((unsigned)r << 12), slab + (((unsigned long long)(hi & ~sel_mask) << chunk_shift) + lor));
         }
         cp_async_arrive_noinc(full_u + 8 * fs);
         // next item of this group's fill sequence: same batch -> masked add of the deposited stride
