@@ -255,7 +255,7 @@ def sharded_parity_check(xb, dist, torch, rank, world, local_rank):
     zs = np.concatenate([za << np.uint64(n - nA), zbm])
     cs = np.concatenate([ca, cb])
     be.set_hamiltonian(xs, zs, cs)
-    e0, it, res = be.lanczos_ground(tol=1e-12, max_iter=600, seed=3)
+    e0, it, res = be.lanczos_ground(tol=1e-10, max_iter=3000, seed=3)
     if rank == 0:
         from scipy.sparse.linalg import LinearOperator, eigsh
 

@@ -49,7 +49,7 @@ def _worker(rank, world, comm_id, n, T, seed, engine, lanczos, out_q):
 
 
 @pytest.mark.skipif(_n_gpus() < 2, reason="needs 2 GPUs")
-@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("n,T,seed,engine,lanczos", [(14, 40, 3, "tile", True), (16, 60, 4, "stream", False),
                                                      (15, 25, 5, "tile", True), (18, 30, 6, "tile", False)])
 def test_shards_match_oracle(n, T, seed, engine, lanczos, world):
@@ -138,7 +138,7 @@ def _gate_worker(rank, world, comm_id, n, seed, out_q):
 
 
 @pytest.mark.skipif(_n_gpus() < 2, reason="needs 2 GPUs")
-@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("world", [2, 4, 8])
 def test_gates_on_sharded_qubits_match_oracle(world):
     """Ansatz gates and fused Pauli rotations that touch the shard bits (pair exchange over NCCL send/recv)."""
     import torch.multiprocessing as mp
