@@ -615,7 +615,7 @@ def main():
     ap.add_argument("--tile-bits", type=int, default=12, choices=[11, 12], help="tile engine: 12 = 4096-amplitude tiles, 11 = 2048 double-buffered")
     ap.add_argument("--expect-kernel", default="auto", choices=["auto", "pipe", "ring", "classic"])
     ap.add_argument("--dispatch", type=int, default=1, choices=[0, 1, 2, 3])
-    ap.add_argument("--planner", type=int, default=2, choices=[1, 2], help="tile planner version (csrc/tile_plan.hpp)")
+    ap.add_argument("--planner", type=int, default=3, choices=[1, 2, 3], help="tile planner version (csrc/tile_plan.hpp)")
     ap.add_argument("--chunk-bits", type=int, default=3, help="tile engine: log2 contiguous amplitudes per HBM chunk")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -47,7 +47,7 @@ def _worker(rank, world, port, n, T, seed, q):
     psi = rng.normal(size=1 << n) + 1j * rng.normal(size=1 << n)
     psi /= np.linalg.norm(psi)
     B, G, Tt = tp.get_plan(n, 3, xm, zm, cf)
-    part = tp.replay(n, 3, B, G, Tt, psi, tile_begin=tb, tile_count=tc)
+    part = tp.replay_records(n, 3, B, tp.get_records(n, 3, xm, zm, cf), Tt, psi, tile_begin=tb, tile_count=tc)
     tot = torch.tensor([part], dtype=torch.float64)
     dist.all_reduce(tot, op=dist.ReduceOp.SUM)
     # the capacity-scaling decomposition b200vqe_expectation uses on a sharded handle: per x_rank class the pair register

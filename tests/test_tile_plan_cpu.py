@@ -13,12 +13,13 @@ import xaccvqe_b200 as xb
 TILE_BITS = 12
 BATCH_DT = np.dtype([("basis", "<u4", 10), ("seg", "<u4", 11), ("g_begin", "<i4"), ("g_end", "<i4"),
                      ("t_begin", "<i4"), ("t_end", "<i4"), ("cls_end", "<i4", 5), ("r_begin", "<i4"), ("r_end", "<i4"),
-                     ("lam", "<u4", 4), ("pad", "<u4", 4)])
+                     ("lam", "<u4", 4), ("pad", "<u4", 4), ("vcol", "<u2", (6, 12)), ("n_views", "<u4"), ("pad2", "<u4", 3)])
 GROUP_DT = np.dtype([("kb", "<u4"), ("n_even", "<u4"), ("n_odd", "<u4"), ("xv", "<u2"), ("hsel", "<i2")])
 TERM_DT = np.dtype([("packed", "<u8"), ("u", "<f8")])
-REC_DT = np.dtype([("kb", "<u4"), ("count", "<u4"), ("xv", "<u2"), ("key", "u1"), ("pad0", "u1"), ("pad1", "<u4"),
+REC_DT = np.dtype([("kb", "<u4"), ("count", "<u4"), ("xv", "<u2"), ("key", "u1"), ("pad0", "u1"), ("view", "<u4"),
                    ("packed0", "<u8"), ("u0", "<f8")])
 STAGE_RECS, STAGE_TERMS = 128, 256          # capacities of one batch (kStageRecs / kStageTerms in csrc/tile_plan.hpp)
+MAX_VIEWS, KEY_VIEW = 6, 0xFE               # kTileMaxViews, kTileRecKeyView
 
 
 def get_records(n, c, xm, zm, cf, tb=12):
@@ -46,7 +47,7 @@ def get_plan(n, c, xm, zm, cf, tb=12):
     args = (C.c_int(n), C.c_int(c), C.c_int(tb), C.c_int64(len(xm)), vp(xm), vp(zm), vp(cr), vp(ci), C.byref(nb), C.byref(ng), C.byref(nt))
     assert lib.b200vqe_debug_tile_plan(*args, None, None, None) == 0
     B, G, T = np.zeros(nb.value, BATCH_DT), np.zeros(ng.value, GROUP_DT), np.zeros(nt.value, TERM_DT)
-    assert BATCH_DT.itemsize == 160 and GROUP_DT.itemsize == 16 and TERM_DT.itemsize == 16
+    assert BATCH_DT.itemsize == 320 and GROUP_DT.itemsize == 16 and TERM_DT.itemsize == 16
     assert lib.b200vqe_debug_tile_plan(*args, vp(B), vp(G), vp(T)) == 0
     return B, G, T
 
@@ -121,8 +122,10 @@ def replay(n, c, B, G, T, psi, tile_begin=0, tile_count=None):
 
 
 def replay_records(n, c, B, R, T, psi, tb=12, tile_begin=0, tile_count=None):
-    """What k_tile_expect computes from the TileRec records: per record, the key fixes WHICH (even / odd nY) and XR (the
-    register part of the flip mask); XR != 0 visits the 8 registers with bit HS = top bit of XR clear, XR == 0 visits all."""
+    """What k_tile_expect / k_tile_expect_pipe compute from the TileRec records: per record, the key fixes WHICH (even / odd nY)
+    and XR (the register part of the flip mask); XR != 0 visits the 8 registers with bit HS = top bit of XR clear, XR == 0 visits
+    all.  A marker record (key 0xfe) switches to another VIEW of the tile: (thread t, register r) then holds the element at byte
+    XOR_{i in t} vcol[view][i] ^ XOR_{j in r} vcol[view][8 + j] of the tile as laid out in shared memory (view 0)."""
     M = tb - c
     n_tiles = 1 << (n - tb)
     tile_count = n_tiles if tile_count is None else tile_count
@@ -132,8 +135,21 @@ def replay_records(n, c, B, R, T, psi, tb=12, tile_begin=0, tile_count=None):
     total = 0.0
     for b in B:
         recs = R[b["r_begin"]:b["r_end"]]
-        assert len(recs) <= STAGE_RECS and b["t_end"] - b["t_begin"] <= STAGE_TERMS
-        assert list(recs["key"]) == sorted(recs["key"]) and np.all(recs["pad0"] == 0)
+        assert len(recs) <= STAGE_RECS + MAX_VIEWS and b["t_end"] - b["t_begin"] <= STAGE_TERMS
+        assert 1 <= b["n_views"] <= MAX_VIEWS and np.all(recs["pad0"] == 0)
+        assert [int(x) >> 4 for x in b["vcol"][0][:tb]] == [1 << i for i in range(tb)]  # view 0: the shared-memory layout itself
+        real = recs[recs["key"] != KEY_VIEW]
+        order = list(zip(real["view"], real["key"]))
+        assert order == sorted(order) and sorted(set(real["view"]) | {0}) == list(range(int(b["n_views"])))
+        vmap = []                                   # per view: virtual index (t | r << 8) -> index into the tile as laid out
+        for k in range(int(b["n_views"])):
+            m = np.zeros(1 << tb, np.uint64)
+            for i in range(tb):
+                m ^= np.where((v >> np.uint64(i)) & np.uint64(1), np.uint64(b["vcol"][k][i]), np.uint64(0)).astype(np.uint64)
+            assert np.all(m & np.uint64(15) == 0) and len(set(m.tolist())) == 1 << tb
+            # the 8 lanes of a quarter-warp (thread bits 0..2) read 8 different 16-byte columns of one row: no bank conflicts
+            assert np.all(((m[1] ^ m[0]) >> np.uint64(4)) & np.uint64(7) != 0) if c >= 3 else True
+            vmap.append((m >> np.uint64(4)).astype(np.int64))
         combo = np.zeros(1 << tb, np.uint64)
         for i in range(M):
             combo ^= np.where((mu >> np.uint64(i)) & np.uint64(1), np.uint64(b["basis"][i]), np.uint64(0)).astype(np.uint64)
@@ -142,10 +158,18 @@ def replay_records(n, c, B, R, T, psi, tb=12, tile_begin=0, tile_count=None):
             for i in range(11):
                 rep |= (t & int(b["seg"][i])) << i
             j = ((np.uint64(rep) ^ combo) << np.uint64(c)) | (lo ^ shear(b, v, tb - 8))
-            tile = psi[j.astype(np.int64)]
+            tile0 = psi[j.astype(np.int64)]
+            view = 0
+            tile = tile0
             for rec in recs:
                 key, xv = int(rec["key"]), int(rec["xv"])
+                if key == KEY_VIEW:
+                    assert int(rec["view"]) > view and rec["count"] == 0
+                    view = int(rec["view"])
+                    tile = tile0[vmap[view]]
+                    continue
                 which, xr, pure = (key >> 4) & 1, ((key & 15) + 1) & 15, key >> 5
+                assert int(rec["view"]) == view and (pure or view == 0)
                 assert xr == xv >> 8 and rec["count"] >= 1 and pure == int((xv & 0xFF) == 0)
                 assert b["t_begin"] <= rec["kb"] and rec["kb"] + rec["count"] <= b["t_end"]
                 assert T[rec["kb"]]["packed"] == rec["packed0"] and T[rec["kb"]]["u"] == rec["u0"]
@@ -299,15 +323,16 @@ def random_hamiltonian(n, T, seed, weights=None):
     (14, 120, 3, 6, (0.7, 0.1, 0.1, 0.1)),      # low-weight strings: many groups share a small subspace
     (13, 80, 4, 7, (0.55, 0.0, 0.0, 0.45)),     # diagonal only
 ])
-@pytest.mark.parametrize("planner", [2, 1])
+@pytest.mark.parametrize("planner", [3, 2, 1])
 def test_plan_replay_matches_oracle(n, T, c, seed, weights, planner):
-    """planner 2 (default): collision-greedy subspaces, register subspace spanned by member masks (shear + pure records);
+    """planner 3 (default of the pipelined kernel): planner 2 + several register subspaces (views) per batch;
+    planner 2: collision-greedy subspaces, register subspace spanned by member masks (shear + pure records);
     planner 1: next-unassigned subspaces, reduced-basis coordinates."""
     xb.capi.lib().b200vqe_debug_set_planner(planner)
     try:
         _plan_replay_matches_oracle(n, T, c, seed, weights, planner)
     finally:
-        xb.capi.lib().b200vqe_debug_set_planner(2)
+        xb.capi.lib().b200vqe_debug_set_planner(3)
 
 
 def _plan_replay_matches_oracle(n, T, c, seed, weights, planner):
@@ -318,15 +343,23 @@ def _plan_replay_matches_oracle(n, T, c, seed, weights, planner):
     B, G, Tt = get_plan(n, c, xm, zm, cf)
     assert len(G) == len(set(int(x) for x in xm)) and len(Tt) == len(xm)
     assert B["g_end"][-1] == len(G) and B["g_begin"][0] == 0
-    e = replay(n, c, B, G, Tt, psi)
     eo, _ = co.expect(n, xm, zm, cf, psi)
-    assert abs(e - eo.real) < 1e-11 * np.abs(cf).sum()
+    if np.all(B["n_views"] == 1):       # the group tables are in view coordinates; the group replay knows view 0 only
+        e = replay(n, c, B, G, Tt, psi)
+        assert abs(e - eo.real) < 1e-11 * np.abs(cf).sum()
+    else:
+        assert planner == 3
     R = get_records(n, c, xm, zm, cf)
     er = replay_records(n, c, B, R, Tt, psi)
     assert abs(er - eo.real) < 1e-11 * np.abs(cf).sum()
     if planner == 1:
         assert not np.any(B["lam"])
-    elif weights is None and T >= 30 and c <= 5:
+    if planner < 3:
+        assert np.all(B["n_views"] == 1) and not np.any(R["key"] == KEY_VIEW)
+    elif weights is None and T >= 40 and c <= 3:
+        # unstructured masks: further views turn most of the remaining records into pure-register records
+        assert np.any(B["n_views"] > 1) and np.sum(R["key"] < 32) < 0.25 * len(R)
+    if planner >= 2 and weights is None and T >= 30 and c <= 5:
         # unstructured masks: the register subspace is spanned by member masks, so some records need no partner read
         assert np.sum(R["key"] >= 32) >= len(B)
     # 2048-amplitude tiles (3 register bits) of the double-buffered kernel
@@ -385,8 +418,12 @@ def test_batch_capacity_splits_large_groups_and_batches():
     cf = rng.normal(size=len(xm)).astype(complex)
     psi = rng.normal(size=1 << n) + 1j * rng.normal(size=1 << n)
     psi /= np.linalg.norm(psi)
-    B, G, Tt = get_plan(n, c, xm, zm, cf)
-    R = get_records(n, c, xm, zm, cf)
+    xb.capi.lib().b200vqe_debug_set_planner(2)       # the group replay below knows one register subspace per batch
+    try:
+        B, G, Tt = get_plan(n, c, xm, zm, cf)
+        R = get_records(n, c, xm, zm, cf)
+    finally:
+        xb.capi.lib().b200vqe_debug_set_planner(3)
     assert len(Tt) == len(xm) and len(G) > len(xs) + 1 and len(B) >= 3
     assert max(int(b["t_end"] - b["t_begin"]) for b in B) <= STAGE_TERMS
     eo, _ = co.expect(n, xm, zm, cf, psi)

@@ -378,7 +378,7 @@ int b200vqe_set_option(b200vqe_handle h, const char *key, const char *value) {
     }
     if (k == "tile-planner") {
         const int c = atoi(value);
-        if (c != 1 && c != 2) FAIL(B200VQE_EINVAL, "tile-planner must be 1 or 2");
+        if (c < 1 || c > 3) FAIL(B200VQE_EINVAL, "tile-planner must be 1, 2 or 3");
         h->opt_tile_planner = c;
         return 0;
     }

@@ -37,7 +37,7 @@ struct DeviceHam {
     // per-term path (host copies, sorted by xmask): caller index, masks, r_k
     std::vector<int64_t> pt_idx; std::vector<uint64_t> pt_x, pt_z; std::vector<int> pt_ny;
     // tile engine (kernels_tile.cuh): batches of xmask groups evaluated per HBM read of the state
-    int tile_C = 0, tile_M = 0, tile_TB = kTileBits, n_tile_batches = 0, n_tile_groups = 0, tile_dispatch = 0;
+    int tile_C = 0, tile_M = 0, tile_TB = kTileBits, n_tile_batches = 0, n_tile_groups = 0, tile_dispatch = 0, tile_views = 1;
     TileBatch *tl_batches = nullptr; TileRec *tl_recs = nullptr; TileTerm *tl_terms = nullptr;
     std::vector<int64_t> tl_term_idx;   // plan term -> caller index (per-term output of the tile engine)
     std::vector<double> tl_term_u;      // unweighted coefficient of the plan term: coef (even nY) | i*coef (odd nY)
@@ -46,7 +46,10 @@ struct DeviceHam {
     // (tl_src keeps the terms until then); <psi|H|psi> itself uses one plan per x_rank class (which peer slab the partners live
     // in), built over the PAIR REGISTER {own slab, slab of rank ^ x_rank} of nl + 1 qubits (class 0: the own slab, nl qubits)
     struct TlSrc { uint64_t x, z; double u; int ny; int64_t idx; };
-    std::vector<TlSrc> tl_src; bool tl_built = false, tl_wanted = false;
+    std::vector<TlSrc> tl_src; bool tl_wanted = false;
+    // the per-term output has its own full-register plan (one register subspace per batch), built on its first use
+    bool tp_built = false; int tp_C = 0, tp_M = 0, n_tp_batches = 0;
+    TileBatch *tp_batches = nullptr; TileRec *tp_recs = nullptr; TileTerm *tp_terms = nullptr;
     struct ExpectClass { int x_rank; int n_reg; int b_begin, b_end; };
     std::vector<ExpectClass> tc_classes;
     TileBatch *tc_batches = nullptr; TileRec *tc_recs = nullptr; TileTerm *tc_terms = nullptr; int n_tc_batches = 0;
@@ -69,6 +72,8 @@ struct DeviceHam {
         cudaFree(tl_batches); cudaFree(tl_recs); cudaFree(tl_terms);
         cudaFree(tc_batches); cudaFree(tc_recs); cudaFree(tc_terms);
         tc_batches = nullptr; tc_recs = nullptr; tc_terms = nullptr;
+        cudaFree(tp_batches); cudaFree(tp_recs); cudaFree(tp_terms);
+        tp_batches = nullptr; tp_recs = nullptr; tp_terms = nullptr; tp_built = false;
         cudaFree(ta_batches); cudaFree(ta_recs); cudaFree(ta_terms);
         cudaFree(sw_batch); cudaFree(sw_groups); cudaFree(sw_terms);
         sw_batch = nullptr; sw_groups = nullptr; sw_terms = nullptr;
@@ -115,6 +120,6 @@ struct b200vqe_ctx {
     int opt_shard_exchange = 0;         // tile H psi on a sharded register: 0 all-gather (auto), 1 pairwise pipeline, 2 needed slabs only (one send/recv group)
     int opt_expect_kernel = 0;          // <psi|H|psi> on 4096-amplitude tiles: 0 pipelined kernel (k_tile_expect_pipe: 3-stage cp.async ring), 1 k_tile_expect, 2 k_tile_expect_ring (bulk-copy ring, C = 3)
     int opt_tile_dispatch = 1;          // record dispatch of k_tile_expect: 0 key-test chain, 1 jump table per record, 2 chain without pure-register records
-    int opt_tile_planner = 2;           // tile planner version (tile_plan.hpp: 2 = collision-greedy subspaces + sheared register subspace, 1 = first version)
+    int opt_tile_planner = 3;           // tile planner version (tile_plan.hpp: 3 = 2 + several register subspaces (views) per batch, 2 = collision-greedy subspaces + sheared register subspace, 1 = first version)
     int opt_tile_chunk_bits = 3;        // C: contiguous amplitudes per chunk = 2^C (128 B at C = 3)
 };

@@ -33,8 +33,9 @@ constexpr int kRingTileBytes = (int)sizeof(double2) << kTileBits;
 
 struct RingTables {                                              // per consumer group
     TileBatch sb;
-    int4 recs[2 * (kStageRecs + 1)];
+    int4 recs[2 * (kStageRecs + kTileMaxViews + 1)];             // records + view markers + the end sentinel
     double2 terms[kStageTerms];
+    uint16_t vbase[kTileMaxViews][kBlock];                       // byte offset of (thread, register 0) of every view of the batch
 };
 constexpr int kRingSmemBytes = kRingStages * kRingTileBytes + kRingGroups * (int)sizeof(RingTables) + 2 * kRingStages * 8 + 64 * 8;
 
@@ -255,7 +256,7 @@ k_tile_expect_ring(const double2 *__restrict__ psi, int M, const TileBatch *__re
                 if (!(k & 1)) q.x -= tb.sb.t_begin;
                 tb.recs[k] = q;
             }
-            if (v0 == 0) tb.recs[2 * n_r] = make_int4(0, 0, 0xff << 16, 0);
+            if (v0 == 0) tb.recs[2 * n_r] = make_int4(0, 0, kTileRecKeyEnd << 16, 0);
             const double2 *tsrc = reinterpret_cast<const double2 *>(terms) + tb.sb.t_begin;
             for (int k = (int)v0; k < n_t; k += kBlock) tb.terms[k] = tsrc[k];
             sh.lm0 = tb.sb.lam[0] << 4; sh.lm1 = tb.sb.lam[1] << 4; sh.lm2 = tb.sb.lam[2] << 4; sh.lm3 = tb.sb.lam[3] << 4;
@@ -331,6 +332,16 @@ __device__ __forceinline__ void cp_async16_u(unsigned dst, const void *src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
 }
 
+__device__ __forceinline__ unsigned lds_u16(unsigned addr) {
+    unsigned short v;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ uint2 lds_u32x2(unsigned addr) {
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+    return v;
+}
 __device__ __forceinline__ int4 lds_i4(unsigned addr) {
     int4 v;
     asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
@@ -391,14 +402,14 @@ __device__ __forceinline__ void pipe_one(const double2 (&a)[16], unsigned tile_u
 }
 
 // all records of the batch: one dispatch per RUN of equal keys (records are sorted by key)
-__device__ __forceinline__ void pipe_walk(const double2 (&a)[16], unsigned tile_u, unsigned v0, unsigned rep, unsigned recs_u, unsigned terms_u,
+// up to the next view marker or the end sentinel, which is returned (ru: its address)
+__device__ __forceinline__ int4 pipe_walk(const double2 (&a)[16], unsigned tile_u, unsigned v0, unsigned rep, unsigned &ru, unsigned terms_u,
                                           double &acc) {
-    unsigned ru = recs_u;
     int4 ra = lds_i4(ru);
 #pragma unroll 1
     for (;;) {
         const unsigned key = (unsigned)ra.z >> 16;
-        if (key >= 2u * kTileRecKeys) break;                          // sentinel
+        if (key >= 2u * kTileRecKeys) break;                          // view marker or end sentinel
 #define B200VQE_CASE(K)                                                                        \
         case K:                                                                                \
             do {                                                                               \
@@ -415,6 +426,7 @@ __device__ __forceinline__ void pipe_walk(const double2 (&a)[16], unsigned tile_
 #undef B200VQE_CASE8
 #undef B200VQE_CASE
     }
+    return ra;
 }
 
 struct PipeFillBatch {               // what a fill needs of its batch (shared memory, per group)
@@ -456,6 +468,7 @@ k_tile_expect_pipe(const double2 *__restrict__ psi, const double2 *__restrict__ 
     RingTables &tb = tabs[g];
     PipeFillBatch &fb = fbs[g];
     const unsigned recs_u = smem_u32(tb.recs), terms_u = smem_u32(tb.terms);
+    const unsigned vbase_u = smem_u32(tb.vbase), vcol_u = smem_u32(tb.sb.vcol);
     const unsigned long long step = (unsigned long long)kRingGroups * gridDim.x;
     // pair register of a sharded <psi|H|psi> (backend_ham.inc): chunks whose high index has bit sel_mask set live in the
     // slab received from the peer rank (psi_hi), the others in this rank's own slab; sel_mask = 0: one register
@@ -531,20 +544,43 @@ k_tile_expect_pipe(const double2 *__restrict__ psi, const double2 *__restrict__ 
                 if (!(k & 1)) q.x -= tb.sb.t_begin;
                 tb.recs[k] = q;
             }
-            if (v0 == 0) tb.recs[2 * n_r] = make_int4(0, 0, 0xff << 16, 0);
+            if (v0 == 0) tb.recs[2 * n_r] = make_int4(0, 0, kTileRecKeyEnd << 16, 0);
             const double2 *tsrc = reinterpret_cast<const double2 *>(terms) + tb.sb.t_begin;
             for (int k = (int)v0; k < n_t; k += kBlock) tb.terms[k] = tsrc[k];
             piv = tb.sb.pad[0];
             dstep = tile_rep(tb.sb, (unsigned)step);
+            {   // where this thread's registers live in every view of the batch (read back by this thread only)
+                const int nv = (int)tb.sb.n_views;
+                for (int k = 0; k < nv; ++k) {
+                    unsigned bs = 0;
+#pragma unroll
+                    for (int b = 0; b < kTileThreadBits; ++b) if ((v0 >> b) & 1u) bs ^= tb.sb.vcol[k][b];
+                    tb.vbase[k][v0] = (uint16_t)bs;
+                }
+            }
             group_sync(g);
             rep = tile_rep(tb.sb, (unsigned)(tile_begin + cur.t));
         }
         mbar_wait(full_u + 8 * s, u & 1u);                  // the tile has landed (all 256 copying threads' cp.async are complete)
         const unsigned tile_u = tiles_u + (unsigned)s * kRingTileBytes;
-        double2 a[16];
+        {
+            unsigned ru = recs_u, view = 0;
+#pragma unroll 1
+            for (;;) {
+                // registers of this view: 16 amplitudes of the tile at  base ^ (XOR of the view's register columns)
+                const unsigned base = lds_u16(vbase_u + ((view << 8) + v0) * 2u);
+                const uint2 gc = lds_u32x2(vcol_u + view * 24u + 16u);      // four 16-bit register columns
+                const unsigned g0 = gc.x & 0xffffu, g1 = gc.x >> 16, g2 = gc.y & 0xffffu, g3 = gc.y >> 16;
+                double2 a[16];
 #pragma unroll
-        for (int r = 0; r < 16; ++r) a[r] = lds_f64x2(tile_u + (v0 << 4) + ((unsigned)r << 12));
-        pipe_walk(a, tile_u, v0, rep, recs_u, terms_u, acc);
+                for (int r = 0; r < 16; ++r)
+                    a[r] = lds_f64x2(tile_u + (base ^ ((r & 1) ? g0 : 0u) ^ ((r & 2) ? g1 : 0u) ^ ((r & 4) ? g2 : 0u) ^ ((r & 8) ? g3 : 0u)));
+                const int4 stop = pipe_walk(a, tile_u, v0, rep, ru, terms_u, acc);
+                if (((unsigned)stop.z >> 16) != (unsigned)kTileRecKeyView) break;
+                view = (unsigned)stop.w;                    // marker: the records that follow want the registers of this view
+                ru += 32;
+            }
+        }
         // the stage is refilled by this same group: a barrier of the group is all the release it needs
         if (i + kRingStages < n_items) {
             group_sync(g);

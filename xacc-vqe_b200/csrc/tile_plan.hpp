@@ -36,8 +36,9 @@ constexpr int kTileThreadBits = 8;   // 256 threads per CTA: virtual bits 0..7 o
 constexpr int kTileMaxDim = 10;      // M = kTileBits - C, C >= 2
 
 constexpr int kTileClasses = 5;      // groups of a batch are ordered by hsel = 0, 1, 2, 3, -1
+constexpr int kTileMaxViews = 6;     // register subspaces ("views") of one batch, view 0 included (expectation plans, TilePlanOpts::views)
 
-struct TileBatch {                   // 160 bytes
+struct TileBatch {                   // 320 bytes
     uint32_t basis[kTileMaxDim];     // basis[i] <-> virtual bit C + i; acts on the high index (j >> C), n - C <= 32
     uint32_t seg[kTileMaxDim + 1];   // coset representative of tile t:  rep = OR_i (t & seg[i]) << i  (zeros at the pivots)
     int32_t g_begin, g_end;          // groups of this batch
@@ -47,8 +48,17 @@ struct TileBatch {                   // 160 bytes
     uint32_t lam[4];                 // shear: register r of a thread holds the amplitude with low index bits lo ^ Lambda(r),
                                      // Lambda(r) = XOR of lam[k] over the set bits k of r (0 for plans built without shear)
     uint32_t pad[4];                 // pad[0] = pivot mask of the subspace (bits of the high index the tile number skips)
+    // Views.  The tile sits in shared memory in the layout of view 0: element (thread t0, register r0) at byte (r0 << 12) | (t0 << 4).
+    // In view k a thread keeps 16 OTHER amplitudes of the tile in its registers: (thread t, register r) of view k is the element at
+    // byte  XOR_{i in t} vcol[k][i]  ^  XOR_{j in r} vcol[k][8 + j]  (a GF(2)-linear map; view 0: the identity, vcol[0][i] = 16 << i),
+    // chosen so that the flip masks of four more xmask groups lie in the register subspace (pure-register records, no partner
+    // reads).  The thread bits that carry the low index bits of a chunk are the same in every view, so the 8 lanes of a
+    // quarter-warp still read the 8 different 16-byte columns of one 128-byte line (no bank conflicts).
+    uint16_t vcol[kTileMaxViews][12];
+    uint32_t n_views;                // >= 1
+    uint32_t pad2[3];
 };
-constexpr int kTileBatchWords = 40;
+constexpr int kTileBatchWords = 80;
 static_assert(sizeof(TileBatch) == 4 * kTileBatchWords, "TileBatch layout");
 
 struct TileGroup {                   // 16 bytes
@@ -76,14 +86,17 @@ struct TileRec {                     // 32 bytes
     uint16_t xv;
     uint8_t key;
     uint8_t pad0;
-    uint32_t pad1;
+    uint32_t view;                   // the view this record is evaluated in (0 unless the plan has views); a record with
+                                     // key kTileRecKeyView is a marker: "load the registers of view `view`", no terms
     uint64_t packed0;                // terms[kb].packed
     double u0;                       // terms[kb].u
 };
 static_assert(sizeof(TileRec) == 32, "TileRec layout");
 
 constexpr int kTileRecKeys = 32;      // (which, XR) combinations; + 32: pure-register records (expectation engine)
-constexpr int kStageRecs = 128;      // records / terms of one batch staged in shared memory by k_tile_expect;
+constexpr int kTileRecKeyView = 0xfe; // marker record between the records of two views
+constexpr int kTileRecKeyEnd = 0xff;  // sentinel the kernels append after the last record of a batch
+constexpr int kStageRecs = 128;      // records / terms of one batch staged in shared memory by k_tile_expect (+ kTileMaxViews markers);
 constexpr int kStageTerms = 256;     // expectation plans are built with these as per-batch capacities
 constexpr int kStageGroupsCap = kStageRecs / 2;
 
@@ -96,6 +109,8 @@ struct TilePlan {
     std::vector<TileTerm> terms;
     std::vector<int64_t> term_src;   // plan term -> index into the input array
     std::vector<TileRec> recs;       // expectation engine only (build_tile_records)
+    std::vector<uint8_t> group_view; // per group: the view its xv / its terms' z parts are expressed in (all 0 without views)
+    int max_views = 1;               // largest TileBatch::n_views of the plan
 };
 
 // Which tiles (cosets) of every batch a rank of a sharded register evaluates in <psi|H|psi>: a contiguous 1/world share;
@@ -163,6 +178,9 @@ struct TilePlanOpts {
     int tile_bits = kTileBits;
     bool collide = false;
     bool shear = false;
+    int views = 1;                   // (shear only) up to this many register subspaces per batch: after view 0, further views are
+                                     // chosen greedily, each spanned by the full virtual masks of RB members that are not pure yet;
+                                     // a view is opened only when it saves more partner reads than loading its registers costs
 };
 
 namespace tileplan {
@@ -436,6 +454,76 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
                 for (int k = 0; k < RB; ++k) if ((s[j] >> k) & 1) newb[j] ^= rho[k];
         }
 
+        // ---- views: (thread t, register r) <-> U-space vector, U = (coordinates in rr.b) << C | low index bits ----
+        struct View { std::vector<uint64_t> col, inv; };
+        auto make_view = [&](const std::vector<uint64_t> &thr_hi, const std::vector<uint64_t> &reg_u) {
+            View v;
+            for (int i = 0; i < C; ++i) v.col.push_back(1ull << i);                 // thread bits 0..C-1: the low index bits
+            for (int j = 0; j < TD; ++j) v.col.push_back(thr_hi[j] << C);           // thread bits C..7: high-index directions
+            for (int k = 0; k < RB; ++k) v.col.push_back(reg_u[k]);                 // register bits
+            v.inv = invert_columns(v.col, TB);
+            return v;
+        };
+        auto view_coords = [&](const View &v, uint64_t u) {
+            uint64_t m = 0;
+            for (int i = 0; i < TB; ++i) m |= (uint64_t)parity64h(v.inv[i] & u) << i;
+            return m;
+        };
+        std::vector<View> views;
+        {
+            std::vector<uint64_t> thr0(newb.begin(), newb.begin() + TD), reg0;
+            for (int k = 0; k < RB; ++k) reg0.push_back((newb[TD + k] << C) | lam[k]);
+            views.push_back(make_view(thr0, reg0));
+        }
+        std::vector<uint64_t> Vu(NM);              // full virtual flip mask of every member
+        std::vector<int> mview(NM, 0);
+        std::vector<uint32_t> mxv(NM);             // ... in the coordinates of its view: thread part | register part << 8
+        for (size_t k = 0; k < NM; ++k) { Vu[k] = (cc[k] << C) | lo[k]; mxv[k] = (uint32_t)view_coords(views[0], Vu[k]); }
+        if (o.shear && o.views > 1) {
+            constexpr int kViewMinGain = 24;       // partner reads (LDS.128 per thread) a view must save: loading its registers costs 16
+            const uint32_t tmask = (1u << (TB - RB)) - 1;
+            std::vector<char> open(NM);
+            std::vector<int> wgt(NM);
+            for (size_t k = 0; k < NM; ++k) {
+                open[k] = (mxv[k] & tmask) != 0;
+                wgt[k] = gs[members[k]].recs * ((mxv[k] >> (TB - RB)) ? (1 << (RB - 1)) : (1 << RB));
+            }
+            while ((int)views.size() < std::min(o.views, kTileMaxViews)) {
+                Rref rc, rv;
+                std::vector<uint64_t> reg_u;
+                for (int pick = 0; pick < RB; ++pick) {
+                    int best = -1, best_score = -1;
+                    for (size_t k = 0; k < NM; ++k) {
+                        if (!open[k] || !rc.reduce(cc[k])) continue;
+                        Rref t = rv;
+                        t.insert(Vu[k]);
+                        int score = 0;
+                        for (size_t m = 0; m < NM; ++m) if (open[m] && !t.reduce(Vu[m])) score += wgt[m];
+                        if (score > best_score) { best_score = score; best = (int)k; }
+                    }
+                    if (best < 0) break;
+                    rv.insert(Vu[best]);
+                    rc.insert(cc[best]);
+                    reg_u.push_back(Vu[best]);
+                }
+                int gain = 0;
+                for (size_t m = 0; m < NM; ++m) if (open[m] && !rv.reduce(Vu[m])) gain += wgt[m];
+                if (reg_u.empty() || gain < kViewMinGain) break;
+                for (int i = 0; i < dim && (int)reg_u.size() < RB; ++i)
+                    if (rc.reduce(1ull << i)) { rc.insert(1ull << i); reg_u.push_back((1ull << i) << C); }
+                std::vector<uint64_t> thr;
+                for (int i = 0; i < dim && (int)thr.size() < TD; ++i)
+                    if (rc.reduce(1ull << i)) { rc.insert(1ull << i); thr.push_back(1ull << i); }
+                views.push_back(make_view(thr, reg_u));
+                for (size_t m = 0; m < NM; ++m)
+                    if (open[m] && !rv.reduce(Vu[m])) {
+                        mview[m] = (int)views.size() - 1;
+                        mxv[m] = (uint32_t)view_coords(views.back(), Vu[m]);      // thread part 0 by construction
+                        open[m] = 0;
+                    }
+            }
+        }
+
         TileBatch B{};
         for (int i = 0; i < dim; ++i) {
             uint64_t v = 0;
@@ -444,12 +532,10 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
         }
         for (int k = 0; k < 4; ++k) B.lam[k] = lam[k];
         for (int p : rr.piv) B.pad[0] |= 1u << p;      // pivot mask: the coset representative of tile t + s is ((rep | pad[0]) + deposit(s)) & ~pad[0]
-        auto shear_of = [&](unsigned reg) {        // Lambda(reg)
-            uint32_t l = 0;
-            for (int k = 0; k < RB; ++k) if ((reg >> k) & 1) l ^= lam[k];
-            return l;
-        };
-        const std::vector<uint64_t> inv = invert_columns(newb, dim);
+        B.n_views = (uint32_t)views.size();
+        P.max_views = std::max(P.max_views, (int)views.size());
+        for (size_t k = 0; k < views.size(); ++k)
+            for (int i = 0; i < TB; ++i) B.vcol[k][i] = (uint16_t)(view_coords(views[0], views[k].col[i]) << 4);
         std::vector<int> sp(rr.piv.begin(), rr.piv.end());
         std::sort(sp.begin(), sp.end());
         {   // tile index bits [lo_i, hi_i) move up by i = number of pivots below them
@@ -464,29 +550,23 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
         }
         B.g_begin = (int32_t)P.groups.size();
         B.t_begin = (int32_t)P.terms.size();
-        // sheared virtual flip mask of every member
-        std::vector<uint16_t> xvs(NM);
-        for (size_t k = 0; k < NM; ++k) {
-            uint64_t m = 0;
-            for (int i = 0; i < dim; ++i) m |= (uint64_t)parity64h(inv[i] & cc[k]) << i;
-            const unsigned xv = (unsigned)((m << C) | lo[k]);
-            xvs[k] = (uint16_t)(xv ^ shear_of(xv >> (TB - RB)));
-        }
         // order the members by pair-selector class (hsel 0, 1, 2, 3, then -1): one code path per class on the device
         auto class_of = [&](size_t k) {
-            const unsigned xr = (unsigned)xvs[k] >> (TB - RB);
+            const unsigned xr = (unsigned)mxv[k] >> (TB - RB);
             return xr ? 31 - __builtin_clz(xr) : kTileClasses - 1;
         };
         std::vector<size_t> ord(NM);
         for (size_t k = 0; k < NM; ++k) ord[k] = k;
         std::stable_sort(ord.begin(), ord.end(), [&](size_t a, size_t b) { return class_of(a) < class_of(b); });
         for (int c = 0; c < kTileClasses; ++c) B.cls_end[c] = 0;
+        std::vector<uint64_t> Zrr_basis(rr.b.begin(), rr.b.end());
         for (size_t kk = 0; kk < NM; ++kk) {
             const size_t k = ord[kk];
             for (int c = class_of(k); c < kTileClasses; ++c) ++B.cls_end[c];
             const G &g = gs[members[k]];
+            const View &vw = views[mview[k]];
             TileGroup tg{};
-            tg.xv = xvs[k];
+            tg.xv = (uint16_t)mxv[k];
             const unsigned xr = tg.xv >> (TB - RB);
             tg.hsel = xr ? (int16_t)(31 - __builtin_clz(xr)) : (int16_t)-1;
             const double weight = tg.hsel >= 0 ? 2.0 : 1.0;
@@ -494,12 +574,11 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
             for (size_t t = g.tb; t < g.te; ++t) {
                 const TilePlanTermIn &ti = in[order[t]];
                 const uint64_t zhi = ti.z >> C;
-                const uint32_t zlo = (uint32_t)(ti.z & lomask);
-                uint64_t Zv = 0;
-                for (int i = 0; i < dim; ++i) Zv |= (uint64_t)parity64h((uint64_t)B.basis[i] & zhi) << i;
-                unsigned zv = (unsigned)((Zv << C) | zlo);
-                // parity(v_phys & zv) with v_phys = v ^ Lambda(reg(v)):  register bit k of z picks up parity(lam[k] & z_lo)
-                for (int k2 = 0; k2 < RB; ++k2) zv ^= (unsigned)parity64h((uint64_t)(lam[k2] & zlo)) << (TB - RB + k2);
+                // z in U space: coordinate i of the high part = parity(rr.b[i] & z_hi); then one bit per column of the view
+                uint64_t zu = ti.z & lomask;
+                for (int i = 0; i < dim; ++i) zu |= (uint64_t)parity64h(Zrr_basis[i] & zhi) << (C + i);
+                unsigned zv = 0;
+                for (int i = 0; i < TB; ++i) zv |= (unsigned)parity64h(vw.col[i] & zu) << i;
                 TileTerm tt;
                 tt.packed = (zhi & 0xffffffffull) | ((uint64_t)(zv & 0xffu) << 32) |
                             ((uint64_t)((zv >> (TB - RB)) & 0xfu) << 40) |
@@ -510,6 +589,7 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
                 ti.odd ? ++tg.n_odd : ++tg.n_even;
             }
             P.groups.push_back(tg);
+            P.group_view.push_back((uint8_t)mview[k]);
         }
         B.g_end = (int32_t)P.groups.size();
         B.t_end = (int32_t)P.terms.size();
@@ -526,12 +606,14 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
     return build_tile_plan(n, C, in, o);
 }
 
-// The plans the backend builds (planner: 2 = collision-greedy subspaces + sheared register subspace [default],
+// The plans the backend builds (planner: 3 = 2 + several register subspaces (views) per batch [default for the pipelined <psi|H|psi>
+// kernel], 2 = collision-greedy subspaces + sheared register subspace,
 // 1 = the first version: next-unassigned subspaces, reduced-basis coordinates).
 inline TilePlanOpts expect_plan_opts(int tile_bits, int planner = 2) {
     TilePlanOpts o;
     o.pair_weights = true; o.max_groups = kStageGroupsCap; o.max_terms = kStageTerms; o.tile_bits = tile_bits;
     o.collide = planner >= 2; o.shear = planner >= 2;
+    o.views = (planner >= 3 && tile_bits == kTileBits) ? kTileMaxViews : 1;      // only the pipelined 4096-amplitude kernel walks views
     return o;
 }
 inline TilePlanOpts apply_plan_opts(int planner = 2) {
@@ -551,7 +633,8 @@ inline void build_tile_records(TilePlan &P, bool allow_pure = false) {
         for (int g = B.g_begin; g < B.g_end; ++g) {
             const TileGroup &tg = P.groups[g];
             const unsigned xr = tg.xv >> kTileThreadBits;
-            const bool pure = allow_pure && (tg.xv & ((1u << kTileThreadBits) - 1)) == 0;
+            const uint32_t view = (size_t)g < P.group_view.size() ? P.group_view[g] : 0u;
+            const bool pure = (allow_pure || view) && (tg.xv & ((1u << kTileThreadBits) - 1)) == 0;
             for (int which = 0; which < 2; ++which) {
                 const uint32_t cnt = which ? tg.n_odd : tg.n_even;
                 if (!cnt) continue;
@@ -560,14 +643,25 @@ inline void build_tile_records(TilePlan &P, bool allow_pure = false) {
                 r.count = cnt;
                 r.xv = tg.xv;
                 r.key = (uint8_t)((pure ? 32 : 0) + which * 16 + (xr ? xr - 1 : 15));
+                r.view = view;
                 r.packed0 = P.terms[r.kb].packed;
                 r.u0 = P.terms[r.kb].u;
                 rs.push_back(r);
             }
         }
-        std::stable_sort(rs.begin(), rs.end(), [](const TileRec &a, const TileRec &b) { return a.key < b.key; });
+        std::stable_sort(rs.begin(), rs.end(), [](const TileRec &a, const TileRec &b) { return a.view != b.view ? a.view < b.view : a.key < b.key; });
         B.r_begin = (int32_t)P.recs.size();
-        P.recs.insert(P.recs.end(), rs.begin(), rs.end());
+        uint32_t cur_view = 0;
+        for (const TileRec &r : rs) {
+            if (r.view != cur_view) {          // marker: the kernel reloads its registers in the layout of view r.view
+                TileRec m{};
+                m.key = (uint8_t)kTileRecKeyView;
+                m.view = r.view;
+                P.recs.push_back(m);
+                cur_view = r.view;
+            }
+            P.recs.push_back(r);
+        }
         B.r_end = (int32_t)P.recs.size();
     }
 }
