@@ -496,7 +496,7 @@ def run_gpu(args):
     tile = args.engine != "stream"
     kernel_name = (("k_tile_apply" if tile else "k_apply<8,true>") if apply_op else
                    (("k_tile_expect_db<3>" if args.tile_bits == 11 else
-                     {"auto": "k_tile_expect_pipe", "pipe": "k_tile_expect_pipe", "ring": "k_tile_expect_ring",
+                     {"auto": "k_tile_expect_pipe", "pipe": "k_tile_expect_pipe", 
                       "classic": "k_tile_expect<2,false,%d>" % args.dispatch}[args.expect_kernel])
                     if tile else "k_expect_energy<8,true>"))
     # DRAM traffic of the step: the tile engine streams this rank's amplitudes once per batch (pair registers: the peer slab too),
@@ -613,7 +613,7 @@ def main():
     ap.add_argument("--engine", default="auto", choices=["auto", "tile", "stream"], help="<psi|H|psi> kernel family")
     ap.add_argument("--tile-ctas", type=int, default=2, choices=[2, 3], help="tile engine: resident CTAs per SM")
     ap.add_argument("--tile-bits", type=int, default=12, choices=[11, 12], help="tile engine: 12 = 4096-amplitude tiles, 11 = 2048 double-buffered")
-    ap.add_argument("--expect-kernel", default="auto", choices=["auto", "pipe", "ring", "classic"])
+    ap.add_argument("--expect-kernel", default="auto", choices=["auto", "pipe", "classic"])
     ap.add_argument("--dispatch", type=int, default=1, choices=[0, 1, 2, 3])
     ap.add_argument("--planner", type=int, default=3, choices=[1, 2, 3], help="tile planner version (csrc/tile_plan.hpp)")
     ap.add_argument("--chunk-bits", type=int, default=3, help="tile engine: log2 contiguous amplitudes per HBM chunk")

@@ -263,6 +263,41 @@ def test_product_state_expectation_exact(xb):
     assert abs(e.real - np.dot(c, want)) < REL * np.abs(c).sum()
 
 
+def _product_state_terms(xm, zm, a, b):
+    """<P_k> of the product state (x) (cos a_q |0> + e^{i b_q} sin a_q |1>), factor by factor (needs no 2^n vector)."""
+    ex, ey, ez = np.sin(2 * a) * np.cos(b), np.sin(2 * a) * np.sin(b), np.cos(2 * a)
+    want = np.ones(len(xm))
+    for q in range(len(a)):
+        xq, zq = ((xm >> np.uint64(q)) & np.uint64(1)).astype(bool), ((zm >> np.uint64(q)) & np.uint64(1)).astype(bool)
+        want *= np.where(xq & zq, ey[q], np.where(xq, ex[q], np.where(zq, ez[q], 1.0)))
+    return want
+
+
+@pytest.mark.parametrize("T,planner,kernel", [(90, 3, "pipe"), (400, 3, "pipe"), (400, 2, "pipe"), (120, 2, "classic")])
+def test_full_size_register_few_terms_product_state(xb, T, planner, kernel):
+    """BASELINE configs[3] register (28 qubits, 4.3 GB) with FEW terms: the pipelined kernel is then bound by the HBM fill, not
+    by the walk, and its consumer groups run ahead of the fills -- the regime in which a one-barrier-per-stage ring lets a
+    group pass the wait on the previous tile's phase (found by bench.py's guard in round 2).  Exact answer: a product state."""
+    n = 28
+    rng = np.random.default_rng(T)
+    a, b = rng.uniform(0, np.pi, n), rng.uniform(0, 2 * np.pi, n)
+    xm, zm, cf = random_hamiltonian(n, T, 100 + T)
+    ny = np.array([bin(int(x) & int(z)).count("1") for x, z in zip(xm, zm)])
+    c = (cf / (1j ** (ny % 4))).real
+    terms = _product_state_terms(xm, zm, a, b)
+    want = float(np.dot(c, terms))
+    be = xb.Backend(n)
+    be.set_option("tile-planner", planner)
+    be.set_option("expect-kernel", kernel)
+    be.set_hamiltonian(xm, zm, cf)
+    be.product_state(a, b)
+    got = [be.expectation().real for _ in range(3)]
+    # every term is ~1e-7 and the sum cancels further, so the honest scale of the rounding error is sum |c_k <P_k>|
+    assert max(abs(g - want) for g in got) < 1e-10 * np.abs(c * terms).sum(), (got, want)
+    assert got[0] == got[1] == got[2]            # fixed reduction order: bit-identical from run to run
+    del be
+
+
 @pytest.mark.parametrize("n,T,seed", [(6, 30, 1), (10, 80, 2), (14, 120, 3)])
 def test_lanczos_vs_dense(xb, n, T, seed):
     xm, zm, cf = random_hamiltonian(n, T, seed)

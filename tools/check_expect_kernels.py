@@ -22,7 +22,7 @@ psi /= np.linalg.norm(psi)
 eo, _ = co.expect(n, xm, zm, cf, psi)
 scale = np.abs(cf).sum()
 ok = True
-for kern, planner, disp in (("pipe", 3, 1), ("pipe", 2, 1), ("pipe", 1, 1), ("ring", 2, 1), ("classic", 2, 1), ("classic", 2, 0), ("classic", 1, 3)):
+for kern, planner, disp in (("pipe", 3, 1), ("pipe", 2, 1), ("pipe", 1, 1), ("classic", 2, 1), ("classic", 2, 0), ("classic", 1, 3)):
     be = xb.Backend(n, device=0)
     be.set_option("expect-kernel", kern)
     be.set_option("tile-planner", planner)

@@ -242,7 +242,6 @@ static int create_common(int n_qubits, int device, int rank, int world, const ch
         set((const void *)k_tile_expect<2, true, 1>, tile);
         set((const void *)k_tile_expect_db<3>, two_small);
         set((const void *)k_tile_apply, tile);
-        set((const void *)k_tile_expect_ring, kRingSmemBytes);
         set((const void *)k_tile_expect_pipe, kPipeSmemBytes);
         set((const void *)k_sweep_small, tile);
         if (ea != cudaSuccess) return fail(std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(ea), B200VQE_ECUDA);
@@ -366,8 +365,7 @@ int b200vqe_set_option(b200vqe_handle h, const char *key, const char *value) {
     if (k == "expect-kernel") {
         if (v == "auto" || v == "pipe") h->opt_expect_kernel = 0;
         else if (v == "classic") h->opt_expect_kernel = 1;
-        else if (v == "ring") h->opt_expect_kernel = 2;
-        else FAIL(B200VQE_EINVAL, "expect-kernel must be auto, pipe, ring or classic");
+        else FAIL(B200VQE_EINVAL, "expect-kernel must be auto, pipe or classic");
         return 0;
     }
     if (k == "tile-dispatch") {

@@ -1,22 +1,26 @@
-// <psi|H|psi> on the tile engine, pipelined:  k_tile_expect_ring.
+// <psi|H|psi> on the tile engine, pipelined:  k_tile_expect_pipe.
 //
 // k_tile_expect (kernels_tile.cuh) fills a tile and walks its records in turn: ld.global x16 -> barrier -> STS x16 ->
 // barrier -> walk.  The ncu source page of that kernel puts 46 % of the warp-stall samples into the per-tile code (the
 // first STS waiting for the loads, the two barriers, two integer divisions and the address arithmetic of the 16 loads).
-// Here the fill is taken off the compute warps altogether:
+// Here the fill is taken off the critical path:
 //
 //   * one CTA per SM, 3 tile buffers of 64 KB in shared memory used as a ring;
-//   * tiles stream from HBM with cp.async.bulk (one bulk copy per 2^C-amplitude chunk, 512 per tile at C = 3, issued by
-//     ONE warp, 16 per lane), completion counted in bytes on the stage's "full" mbarrier;
-//   * TWO groups of 256 threads each own every other tile of the CTA: wait on "full", read their own 16 amplitudes
-//     from the landed tile into registers, walk the batch's records exactly as k_tile_expect does, arrive on the
-//     stage's "empty" mbarrier; the group's first warp then waits for that barrier and streams the CTA's tile i + 3
-//     into the stage just released.  While one group walks tile i and the other tile i+1, tile i+2 is in flight.
-//     (A dedicated 17th producer warp would cost the register budget of four: 96 instead of 128 registers per thread.)
+//   * tiles stream from HBM with cp.async (LDGSTS, 16 B per thread per row: every thread copies exactly the 16 amplitudes
+//     it owns in view 0, so the tile lands in the sheared (thread, register) layout the records are planned for);
+//     completion is an mbarrier per (stage, walking group): cp.async.mbarrier.arrive.noinc by every copying thread;
+//   * TWO groups of 256 threads each own every other tile of the CTA: wait on the barrier, read their 16 amplitudes of
+//     the current VIEW from the landed tile into registers, walk the view's records, switch to the next view (tile_plan.hpp:
+//     another register subspace of the same tile, in which four more xmask groups pair amplitudes of ONE thread), and
+//     finally refill the stage with the CTA's tile i + 3.  While one group walks tile i and the other tile i+1, tile i+2
+//     is in flight.
 //
-// The bulk copies land a chunk in its physical order, so the tile sits in shared memory UNsheared: element (row q,
-// thread t) of the sheared layout the records are planned for (tile_plan.hpp, TileBatch::lam) lives at byte
-// (q << 12) | ((t << 4) ^ (Lambda(q) << 4)).  One extra XOR per shared-memory read; pure-register records read nothing.
+// A bulk-copy (cp.async.bulk / UBLKCP) fill was built and measured in round 2 and removed again: UBLKCP is a
+// uniform-datapath instruction, one copy per warp-instruction with its operands in uniform registers, so a warp whose
+// lanes hold 32 chunk addresses is serialised into an ELECT / R2UR / UBLKCP / BRA.U.ANY loop (~9 issue slots per 128-byte
+// chunk, 512 chunks per tile; > 300 s per step against 1.06 s).  The cosets of a GF(2) subspace are XOR-scattered 128-byte
+// chunks: no larger contiguous run for a bulk copy, no affine tensor map.  Evidence: profiles/r2_sass_ring_and_pipe_fill.txt,
+// profiles/r2_expect_kernel_variants_28q_1e4terms.txt.
 //
 // Work items (batch, tile) are visited without divisions: every role advances its own (batch, tile) pair, and the coset
 // representative of the next tile of the same batch is a masked add:  rep' = ((rep | P) + dstep) & ~P  with P the pivot
@@ -37,7 +41,6 @@ struct RingTables {                                              // per consumer
     double2 terms[kStageTerms];
     uint16_t vbase[kTileMaxViews][kBlock];                       // byte offset of (thread, register 0) of every view of the batch
 };
-constexpr int kRingSmemBytes = kRingStages * kRingTileBytes + kRingGroups * (int)sizeof(RingTables) + 2 * kRingStages * 8 + 64 * 8;
 
 __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
@@ -71,90 +74,6 @@ __device__ __forceinline__ double2 lds_f64x2(unsigned addr) {
     return v;
 }
 
-// Lambda(q) << 4 from the four per-batch generators, q a compile-time constant after unrolling
-__device__ __forceinline__ unsigned shear_bytes(int q, unsigned lm0, unsigned lm1, unsigned lm2, unsigned lm3) {
-    unsigned l = 0;
-    if (q & 1) l ^= lm0;
-    if (q & 2) l ^= lm1;
-    if (q & 4) l ^= lm2;
-    if (q & 8) l ^= lm3;
-    return l;
-}
-
-struct RingShear { unsigned lm0, lm1, lm2, lm3; };
-
-// one half of a record on the ring layout; see tile_rec_half (kernels_tile.cuh) for the arithmetic
-template <int WHICH, int XR, int BV, bool PURE>
-__device__ __forceinline__ void ring_rec_half(const double2 (&a)[16], unsigned Pu, const RingShear &sh, unsigned v0, unsigned rep,
-                                              const int4 ra, const int4 rb, const double2 *__restrict__ s_terms, double &acc) {
-    constexpr int RB = 4;
-    constexpr int HS = XR ? XrInfo<XR>::HS : RB - 1;
-    constexpr int NP = 1 << (RB - 1);
-    double w[NP];
-#pragma unroll
-    for (int i = 0; i < NP; ++i) {
-        const int r = ((i >> HS) << (HS + 1)) | (BV << HS) | (i & ((1 << HS) - 1));
-        const int q = r ^ XR;
-        const double2 b = PURE ? a[q] : lds_f64x2((Pu ^ shear_bytes(q, sh.lm0, sh.lm1, sh.lm2, sh.lm3)) + ((unsigned)q << 12));
-        w[i] = WHICH == 0 ? fma(b.x, a[r].x, b.y * a[r].y) : fma(b.x, a[r].y, -(b.y * a[r].x));
-    }
-    double *none = nullptr;
-    tile_term<RB, HS, BV, false>(w, ((unsigned long long)(unsigned)rb.y << 32) | (unsigned)rb.x, __hiloint2double(rb.w, rb.z), v0, rep, acc, none);
-    const int count = ra.y;
-    if (count > 1) {
-        const double2 *tp = s_terms + ra.x;
-        double2 t = tp[1];
-#pragma unroll 1
-        for (int e = 1; e < count; ++e) {
-            const double2 c = t;
-            if (e + 1 < count) t = tp[e + 1];
-            tile_term<RB, HS, BV, false>(w, (unsigned long long)__double_as_longlong(c.x), c.y, v0, rep, acc, none);
-        }
-    }
-}
-
-template <int K>
-__device__ __forceinline__ void ring_one(const double2 (&a)[16], unsigned tile_u, const RingShear &sh, unsigned v0, unsigned rep,
-                                         const int4 ca, const int4 cb, const double2 *__restrict__ s_terms, double &acc) {
-    constexpr int WHICH = (K >> 4) & 1;
-    constexpr int XR = ((K & 15) + 1) & 15;
-    constexpr bool PURE = K >= kTileRecKeys;
-    if constexpr (!(PURE && XR == 0 && WHICH == 1)) {
-        const unsigned Pu = tile_u + (((v0 ^ (unsigned)ca.z) & 0xffu) << 4);      // row 0 of the partner thread, unsheared
-        ring_rec_half<WHICH, XR, 0, PURE>(a, Pu, sh, v0, rep, ca, cb, s_terms, acc);
-        if (XR == 0) ring_rec_half<WHICH, XR, 1, PURE>(a, Pu, sh, v0, rep, ca, cb, s_terms, acc);
-    }
-}
-
-// all records of the batch: one dispatch per RUN of equal keys (records are sorted by key)
-__device__ __forceinline__ void ring_walk(const double2 (&a)[16], unsigned tile_u, const RingShear &sh, unsigned v0, unsigned rep,
-                                          const int4 *__restrict__ s_recs, const double2 *__restrict__ s_terms, double &acc) {
-    int gi = 0;
-    int4 ra = s_recs[0], rb = s_recs[1];
-#pragma unroll 1
-    for (;;) {
-        const unsigned key = (unsigned)ra.z >> 16;
-        if (key >= 2u * kTileRecKeys) break;                          // sentinel
-#define B200VQE_CASE(K)                                                                        \
-        case K:                                                                                \
-            do {                                                                               \
-                const int4 ca = ra, cb = rb;                                                   \
-                ++gi;                                                                          \
-                ra = s_recs[2 * gi];                                                           \
-                rb = s_recs[2 * gi + 1];                                                       \
-                ring_one<K>(a, tile_u, sh, v0, rep, ca, cb, s_terms, acc);                     \
-            } while (((unsigned)ra.z >> 16) == (unsigned)(K));                                 \
-            break;
-#define B200VQE_CASE8(K) B200VQE_CASE(K) B200VQE_CASE(K + 1) B200VQE_CASE(K + 2) B200VQE_CASE(K + 3) B200VQE_CASE(K + 4) B200VQE_CASE(K + 5) B200VQE_CASE(K + 6) B200VQE_CASE(K + 7)
-        switch (key) {
-            B200VQE_CASE8(0) B200VQE_CASE8(8) B200VQE_CASE8(16) B200VQE_CASE8(24) B200VQE_CASE8(32) B200VQE_CASE8(40) B200VQE_CASE8(48) B200VQE_CASE8(56)
-            default: break;
-        }
-#undef B200VQE_CASE8
-#undef B200VQE_CASE
-    }
-}
-
 // (batch, tile) of a role, advanced without divisions
 struct RingCursor {
     int b;
@@ -164,150 +83,6 @@ struct RingCursor {
         while (t >= tile_count) { t -= tile_count; ++b; }
     }
 };
-
-// One warp streams tile (b, t) into stage s: 512 bulk copies of 128 B (16 per lane), bytes counted on full[s].
-// Chunk (k << 5 | lane) of the tile = high index  rep ^ XOR_i mu_i basis[i]  with mu = k << 5 | lane.
-__device__ __forceinline__ void ring_fill(const double2 *__restrict__ psi, const TileBatch *__restrict__ B, int M, unsigned t_abs,
-                                          unsigned tile_u, unsigned full_bar, int lane) {
-    constexpr int C = 3;
-    unsigned rep = 0;
-#pragma unroll
-    for (int i = 0; i <= kTileMaxDim; ++i) rep |= (t_abs & __ldg(&B->seg[i])) << i;
-    unsigned base = rep;
-#pragma unroll
-    for (int k = 0; k < 5; ++k) if ((lane >> k) & 1) base ^= __ldg(&B->basis[k]);       // chunk coordinate bits 0..4 = lane
-    const unsigned kb0 = __ldg(&B->basis[5]), kb1 = __ldg(&B->basis[6]), kb2 = __ldg(&B->basis[7]), kb3 = M > 8 ? __ldg(&B->basis[8]) : 0u;
-    if (lane == 0) mbar_arrive_expect_tx(full_bar, (unsigned)kRingTileBytes);
-    __syncwarp();
-    const char *psi_b = reinterpret_cast<const char *>(psi);
-    const unsigned dst0 = tile_u + ((unsigned)lane << (C + 4));
-#pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        const unsigned hi = base ^ ((k & 1) ? kb0 : 0u) ^ ((k & 2) ? kb1 : 0u) ^ ((k & 4) ? kb2 : 0u) ^ ((k & 8) ? kb3 : 0u);
-        bulk_g2s(dst0 + ((unsigned)k << (5 + C + 4)), psi_b + ((unsigned long long)hi << (C + 4)), 16u << C, full_bar);
-    }
-}
-
-// C == 3 only (128-byte chunks); grid = number of SMs; dynamic shared memory = kRingSmemBytes.
-// Item i of a CTA (its i-th (batch, tile) pair) lives in stage i % 3 and is walked by group i % 2; when a group has
-// finished item i, its first warp waits for the stage to be released by the whole group and streams item i + 3 into it.
-__global__ void __launch_bounds__(kRingThreads, 1)
-k_tile_expect_ring(const double2 *__restrict__ psi, int M, const TileBatch *__restrict__ batches, int n_batches,
-                   unsigned long long tile_begin, unsigned long long tile_count, const TileRec *__restrict__ recs,
-                   const TileTerm *__restrict__ terms, double *partials, unsigned *counter, double *out) {
-    extern __shared__ __align__(128) unsigned char ring_raw[];
-    unsigned char *tiles = ring_raw;                                                     // [kRingStages][64 KB]
-    RingTables *tabs = reinterpret_cast<RingTables *>(ring_raw + kRingStages * kRingTileBytes);
-    unsigned long long *bars = reinterpret_cast<unsigned long long *>(tabs + kRingGroups);   // full[3], empty[3]
-    double *s_red = reinterpret_cast<double *>(bars + 2 * kRingStages);                   // [16] warp sums
-    const unsigned tiles_u = smem_u32(tiles);
-    const unsigned full_u = smem_u32(bars), empty_u = smem_u32(bars + kRingStages);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < kRingStages; ++s) {
-            mbar_init(full_u + 8 * s, 1);                     // the filling warp's arrive.expect_tx; the copies complete the bytes
-            mbar_init(empty_u + 8 * s, kBlock / 32);          // one arrive per warp of the group that walked the stage
-        }
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    }
-    __syncthreads();
-
-    const unsigned long long total = (unsigned long long)n_batches * tile_count;
-    const unsigned long long n_items = blockIdx.x < total ? (total - blockIdx.x + gridDim.x - 1) / gridDim.x : 0ull;   // once per kernel
-    const int g = warp / (kBlock / 32);
-    const bool leader = (warp % (kBlock / 32)) == 0;
-    const unsigned v0 = threadIdx.x & (kBlock - 1);
-    RingTables &tb = tabs[g];
-    const unsigned long long step = (unsigned long long)kRingGroups * gridDim.x;
-    double acc = 0.0;
-
-    RingCursor fill{0, 0};              // next item this group's first warp streams in (item g + 3 after the prologue)
-    if (leader) {
-        // prologue: items 0 and 2 by group 0, item 1 by group 1
-        for (int j = g; j < kRingStages; j += kRingGroups) {
-            if ((unsigned long long)j < n_items) {
-                RingCursor c{0, 0};
-                c.advance(blockIdx.x + (unsigned long long)j * gridDim.x, tile_count);
-                ring_fill(psi, batches + c.b, M, (unsigned)(tile_begin + c.t), tiles_u + (unsigned)j * kRingTileBytes, full_u + 8 * j, lane);
-            }
-        }
-        fill.advance(blockIdx.x + (unsigned long long)(g + kRingStages) * gridDim.x, tile_count);
-    }
-
-    RingCursor cur{0, 0};
-    cur.advance(blockIdx.x + (unsigned long long)g * gridDim.x, tile_count);
-    int cur_b = -1;
-    unsigned piv = 0, dstep = 0, rep = 0;
-    RingShear sh{0, 0, 0, 0};
-    int s = g;                                              // stage of item i = i % kRingStages, use u = i / kRingStages
-    unsigned u = 0;
-    for (unsigned long long i = g; i < n_items; i += kRingGroups) {
-        if (cur.b != cur_b) {                               // uniform over the group
-            cur_b = cur.b;
-            group_sync(g);                                  // everyone is done with the previous batch's tables
-            if (v0 < kTileBatchWords) reinterpret_cast<uint32_t *>(&tb.sb)[v0] = reinterpret_cast<const uint32_t *>(&batches[cur_b])[v0];
-            group_sync(g);
-            const int n_r = tb.sb.r_end - tb.sb.r_begin, n_t = tb.sb.t_end - tb.sb.t_begin;
-            const int4 *rsrc = reinterpret_cast<const int4 *>(recs + tb.sb.r_begin);
-            for (int k = (int)v0; k < 2 * n_r; k += kBlock) {
-                int4 q = rsrc[k];
-                if (!(k & 1)) q.x -= tb.sb.t_begin;
-                tb.recs[k] = q;
-            }
-            if (v0 == 0) tb.recs[2 * n_r] = make_int4(0, 0, kTileRecKeyEnd << 16, 0);
-            const double2 *tsrc = reinterpret_cast<const double2 *>(terms) + tb.sb.t_begin;
-            for (int k = (int)v0; k < n_t; k += kBlock) tb.terms[k] = tsrc[k];
-            sh.lm0 = tb.sb.lam[0] << 4; sh.lm1 = tb.sb.lam[1] << 4; sh.lm2 = tb.sb.lam[2] << 4; sh.lm3 = tb.sb.lam[3] << 4;
-            piv = tb.sb.pad[0];
-            dstep = tile_rep(tb.sb, (unsigned)step);
-            group_sync(g);
-            rep = tile_rep(tb.sb, (unsigned)(tile_begin + cur.t));
-        }
-        mbar_wait(full_u + 8 * s, u & 1u);                  // the tile has landed
-        const unsigned tile_u = tiles_u + (unsigned)s * kRingTileBytes;
-        double2 a[16];
-        const unsigned own = tile_u + (v0 << 4);
-#pragma unroll
-        for (int r = 0; r < 16; ++r) a[r] = lds_f64x2((own ^ shear_bytes(r, sh.lm0, sh.lm1, sh.lm2, sh.lm3)) + ((unsigned)r << 12));
-        ring_walk(a, tile_u, sh, v0, rep, tb.recs, tb.terms, acc);
-        __syncwarp();
-        if (lane == 0) mbar_arrive(empty_u + 8 * s);       // release: this warp's reads of the stage are complete
-        if (leader && i + kRingStages < n_items) {
-            mbar_wait(empty_u + 8 * s, u & 1u);            // ... and so are the other warps' of the group
-            ring_fill(psi, batches + fill.b, M, (unsigned)(tile_begin + fill.t), tile_u, full_u + 8 * s, lane);
-            fill.advance(step, tile_count);
-        }
-        // next tile of this group: same batch -> masked add of the deposited stride (a new batch recomputes it above)
-        cur.advance(step, tile_count);
-        rep = ((rep | piv) + dstep) & ~piv;
-        s += kRingGroups;
-        if (s >= kRingStages) { s -= kRingStages; ++u; }
-    }
-    const double wsum = warp_sum(acc);
-    if (lane == 0) s_red[warp] = wsum;
-    __syncthreads();
-    // deterministic grid reduction: per-CTA sum in warp order, the last CTA adds the CTAs in order
-    __shared__ bool s_last;
-    if (threadIdx.x == 0) {
-        double sum = 0.0;
-#pragma unroll
-        for (int w = 0; w < kRingGroups * (kBlock / 32); ++w) sum += s_red[w];
-        partials[blockIdx.x] = sum;
-        __threadfence();
-        s_last = atomicAdd(counter, 1u) == gridDim.x - 1;
-    }
-    __syncthreads();
-    if (s_last && threadIdx.x < 32) {
-        __threadfence();
-        double sum = 0.0;
-        for (unsigned b = lane; b < gridDim.x; b += 32) sum += __ldcg(&partials[b]);
-        sum = warp_sum(sum);
-        if (lane == 0) { out[0] = sum; *counter = 0u; }
-    }
-}
-
 
 // ---------------------------------------------------------------------------------------------
 // The same ring filled with cp.async (LDGSTS, 16 B per thread) instead of bulk copies: k_tile_expect_pipe, the default.
@@ -436,7 +211,7 @@ struct PipeFillBatch {               // what a fill needs of its batch (shared m
     uint32_t piv;
     uint32_t pad[6];
 };
-constexpr int kPipeSmemBytes = kRingStages * kRingTileBytes + kRingGroups * (int)(sizeof(RingTables) + sizeof(PipeFillBatch)) + kRingStages * 8 + 32 * 8;
+constexpr int kPipeSmemBytes = kRingStages * kRingTileBytes + kRingGroups * (int)(sizeof(RingTables) + sizeof(PipeFillBatch)) + kRingGroups * kRingStages * 8 + 32 * 8;
 
 __global__ void __launch_bounds__(kRingThreads, 1)
 k_tile_expect_pipe(const double2 *__restrict__ psi, const double2 *__restrict__ psi_hi, unsigned sel_mask, int C, int M,
@@ -447,14 +222,17 @@ k_tile_expect_pipe(const double2 *__restrict__ psi, const double2 *__restrict__ 
     unsigned char *tiles = ring_raw;                                                     // [kRingStages][64 KB]
     RingTables *tabs = reinterpret_cast<RingTables *>(ring_raw + kRingStages * kRingTileBytes);
     PipeFillBatch *fbs = reinterpret_cast<PipeFillBatch *>(tabs + kRingGroups);
-    unsigned long long *bars = reinterpret_cast<unsigned long long *>(fbs + kRingGroups);    // full[3]
-    double *s_red = reinterpret_cast<double *>(bars + kRingStages);                       // [16] warp sums
+    // full[stage][group that walks the item]: a stage is walked by the two groups in turn, and a group must see EVERY phase of a
+    // barrier it waits on (a parity wait cannot tell phase k from phase k + 2: with one barrier per stage a group that ran two
+    // items ahead of a slow fill passed the wait on the previous tile's phase), so each (stage, walker) pair has its own
+    unsigned long long *bars = reinterpret_cast<unsigned long long *>(fbs + kRingGroups);
+    double *s_red = reinterpret_cast<double *>(bars + kRingGroups * kRingStages);         // [16] warp sums
     const unsigned tiles_u = smem_u32(tiles);
     const unsigned full_u = smem_u32(bars);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kRingStages; ++s) mbar_init(full_u + 8 * s, kBlock);      // one (noinc) arrive per copying thread
+        for (int s = 0; s < kRingGroups * kRingStages; ++s) mbar_init(full_u + 8 * s, kBlock);      // one (noinc) arrive per copying thread
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -512,7 +290,7 @@ k_tile_expect_pipe(const double2 *__restrict__ psi, const double2 *__restrict__ 
             const char *slab = (hi & sel_mask) ? psi_h : psi_b;
             cp_async16_u(dst + ((unsigned)r << 12), slab + (((unsigned long long)(hi & ~sel_mask) << chunk_shift) + lor));
         }
-        cp_async_arrive_noinc(full_u + 8 * fs);
+        cp_async_arrive_noinc(full_u + 8 * (kRingGroups * fs + (1 - g)));   // the item is walked by the other group
         // next item of this group's fill sequence: same batch -> masked add of the deposited stride
         fcur.advance(step, tile_count);
         f_rep = ((f_rep | fb.piv) + f_dstep) & ~fb.piv;
@@ -529,8 +307,9 @@ k_tile_expect_pipe(const double2 *__restrict__ psi, const double2 *__restrict__ 
     cur.advance(blockIdx.x + (unsigned long long)g * gridDim.x, tile_count);
     int cur_b = -1;
     unsigned piv = 0, dstep = 0, rep = 0;
-    int s = g;                                              // stage of item i = i % kRingStages, use u = i / kRingStages
-    unsigned u = 0;
+    int s = g;                                              // stage of item i = i % kRingStages
+    unsigned u = 0;                                         // uses of barrier (s, g) so far: every third item of this group
+    int s_wraps = 0;
     for (unsigned long long i = g; i < n_items; i += kRingGroups) {
         if (cur.b != cur_b) {                               // uniform over the group
             cur_b = cur.b;
@@ -561,7 +340,7 @@ k_tile_expect_pipe(const double2 *__restrict__ psi, const double2 *__restrict__ 
             group_sync(g);
             rep = tile_rep(tb.sb, (unsigned)(tile_begin + cur.t));
         }
-        mbar_wait(full_u + 8 * s, u & 1u);                  // the tile has landed (all 256 copying threads' cp.async are complete)
+        mbar_wait(full_u + 8 * (kRingGroups * s + g), u & 1u);     // the tile has landed (all 256 copying threads' cp.async are complete)
         const unsigned tile_u = tiles_u + (unsigned)s * kRingTileBytes;
         {
             unsigned ru = recs_u, view = 0;
@@ -589,7 +368,8 @@ k_tile_expect_pipe(const double2 *__restrict__ psi, const double2 *__restrict__ 
         cur.advance(step, tile_count);
         rep = ((rep | piv) + dstep) & ~piv;
         s += kRingGroups;
-        if (s >= kRingStages) { s -= kRingStages; ++u; }
+        if (s >= kRingStages) s -= kRingStages;
+        if (++s_wraps == kRingStages) { s_wraps = 0; ++u; }      // barrier (s, g) comes round every kRingStages items of this group
     }
     const double wsum = warp_sum(acc);
     if (lane == 0) s_red[warp] = wsum;
