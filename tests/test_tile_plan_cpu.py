@@ -19,7 +19,9 @@ TERM_DT = np.dtype([("packed", "<u8"), ("u", "<f8")])
 REC_DT = np.dtype([("kb", "<u4"), ("count", "<u4"), ("xv", "<u2"), ("key", "u1"), ("pad0", "u1"), ("view", "<u4"),
                    ("packed0", "<u8"), ("u0", "<f8")])
 STAGE_RECS, STAGE_TERMS = 128, 256          # capacities of one batch (kStageRecs / kStageTerms in csrc/tile_plan.hpp)
-MAX_VIEWS, KEY_VIEW = 6, 0xFE               # kTileMaxViews, kTileRecKeyView
+MAX_VIEWS, KEY_VIEW, KEY_FUSED = 6, 0xFE, 0xFD               # kTileMaxViews, kTileRecKeyView, kTileRecKeyFused
+SLOT_DT = np.dtype([("zl", "<u4"), ("zt", "<u4"), ("u", "<f8"), ("s0", "<f8"), ("s1", "<f8"), ("kb", "<u4"), ("pad", "<u4"), ("xv", "<u2"),
+                    ("key", "u1"), ("pad0", "u1"), ("view", "<u4"), ("s2", "<f8"), ("pad2", "<u8")])      # TileFusedSlot
 
 
 def get_records(n, c, xm, zm, cf, tb=12):
@@ -136,11 +138,27 @@ def replay_records(n, c, B, R, T, psi, tb=12, tile_begin=0, tile_count=None):
     for b in B:
         recs = R[b["r_begin"]:b["r_end"]]
         assert len(recs) <= STAGE_RECS + MAX_VIEWS and b["t_end"] - b["t_begin"] <= STAGE_TERMS
-        assert 1 <= b["n_views"] <= MAX_VIEWS and np.all(recs["pad0"] == 0)
+        assert 1 <= b["n_views"] <= MAX_VIEWS
         assert [int(x) >> 4 for x in b["vcol"][0][:tb]] == [1 << i for i in range(tb)]  # view 0: the shared-memory layout itself
-        real = recs[recs["key"] != KEY_VIEW]
+        # split the stream: markers, fused view blocks (4 slots = 8 entries after a marker with count > 0), plain records
+        stream, k = [], 0
+        while k < len(recs):
+            rec = recs[k]
+            if rec["key"] == KEY_VIEW and rec["count"] > 0:
+                slots = recs[k + 1:k + 9].view(SLOT_DT)
+                assert len(slots) == 4 and np.all(slots["key"] == KEY_FUSED) and np.all(slots["view"] == rec["view"])
+                stream.append(("view", rec, slots))
+                k += 9
+            elif rec["key"] == KEY_VIEW:
+                stream.append(("view", rec, None))
+                k += 1
+            else:
+                stream.append(("rec", rec, None))
+                k += 1
+        real = np.array([r for kind, r, _ in stream if kind == "rec"], dtype=REC_DT)
         order = list(zip(real["view"], real["key"]))
-        assert order == sorted(order) and sorted(set(real["view"]) | {0}) == list(range(int(b["n_views"])))
+        views_seen = sorted(set(int(r["view"]) for kind, r, _ in stream) | {0})
+        assert order == sorted(order) and views_seen == list(range(int(b["n_views"]))) and np.all(real["pad0"] == 0)
         vmap = []                                   # per view: virtual index (t | r << 8) -> index into the tile as laid out
         for k in range(int(b["n_views"])):
             m = np.zeros(1 << tb, np.uint64)
@@ -161,18 +179,39 @@ def replay_records(n, c, B, R, T, psi, tb=12, tile_begin=0, tile_count=None):
             tile0 = psi[j.astype(np.int64)]
             view = 0
             tile = tile0
-            for rec in recs:
+            for kind, rec, slots in stream:
                 key, xv = int(rec["key"]), int(rec["xv"])
-                if key == KEY_VIEW:
-                    assert int(rec["view"]) > view and rec["count"] == 0
+                if kind == "view":
+                    assert int(rec["view"]) >= view
                     view = int(rec["view"])
                     tile = tile0[vmap[view]]
+                    if slots is None:
+                        continue
+                    # fused block: slot j pairs register r (bit j clear) with r | 1 << j of the SAME thread; the first NE slots
+                    # take Re w, the others Im w; the sign is (thread constant) x (+-1 per free register bit)
+                    ne = int(rec["count"]) - 1
+                    th, rg = v & np.uint64(0xFF), (v >> np.uint64(8)).astype(np.int64)
+                    for jj, sl in enumerate(slots):
+                        if sl["u"] == 0.0:
+                            continue
+                        assert int(sl["xv"]) == 1 << (8 + jj) and T[int(b["t_begin"]) + int(sl["kb"])]["u"] == sl["u"]
+                        act = ((rg >> jj) & 1) == 0
+                        va = v[act]
+                        a, bb = tile[va.astype(np.int64)], tile[(va | np.uint64(1 << (8 + jj))).astype(np.int64)]
+                        w = np.conj(bb) * a
+                        par = (bin(rep & int(sl["zl"])).count("1") & 1) ^ parity(th[act] & np.uint64(sl["zt"]))
+                        sg = 1.0 - 2.0 * par
+                        free = [q for q in range(4) if q != jj]
+                        for kk, q in enumerate(free):
+                            sg = sg * np.where((rg[act] >> q) & 1, float(sl["s%d" % kk]), 1.0)
+                        total += float(np.sum(sg * float(sl["u"]) * (w.real if jj < ne else w.imag)))
                     continue
                 which, xr, pure = (key >> 4) & 1, ((key & 15) + 1) & 15, key >> 5
                 assert int(rec["view"]) == view and (pure or view == 0)
                 assert xr == xv >> 8 and rec["count"] >= 1 and pure == int((xv & 0xFF) == 0)
-                assert b["t_begin"] <= rec["kb"] and rec["kb"] + rec["count"] <= b["t_end"]
-                assert T[rec["kb"]]["packed"] == rec["packed0"] and T[rec["kb"]]["u"] == rec["u0"]
+                kb = int(b["t_begin"]) + int(rec["kb"])              # record term indices are relative to the batch
+                assert kb + rec["count"] <= b["t_end"]
+                assert T[kb]["packed"] == rec["packed0"] and T[kb]["u"] == rec["u0"]
                 r = v >> np.uint64(8)
                 if xr:
                     hs = xr.bit_length() - 1
@@ -183,7 +222,7 @@ def replay_records(n, c, B, R, T, psi, tb=12, tile_begin=0, tile_count=None):
                 a, bb = tile[va.astype(np.int64)], tile[(va ^ np.uint64(xv)).astype(np.int64)]
                 w = np.conj(bb) * a
                 f = np.zeros(len(va))
-                for k in range(int(rec["kb"]), int(rec["kb"] + rec["count"])):
+                for k in range(kb, kb + int(rec["count"])):
                     packed, u = int(T[k]["packed"]), float(T[k]["u"])
                     p0 = (bin(rep & packed & 0xFFFFFFFF).count("1") & 1) ^ parity(va & np.uint64(0xFF) & np.uint64((packed >> 32) & 0xFF))
                     sr = parity((va >> np.uint64(8)) & np.uint64((packed >> 40) & 0xF))
@@ -242,7 +281,8 @@ def replay_apply(n, c, B, R, T, classes, psi, rank=0, world=1):
                     which, xr = key >> 4, ((key & 15) + 1) & 15
                     assert xr == xv >> 8 and key < 32 and not np.any(b["lam"])      # H psi plans: no shear, no pure records
                     f = np.zeros(1 << TILE_BITS)
-                    for k in range(int(rec["kb"]), int(rec["kb"] + rec["count"])):
+                    kb = int(b["t_begin"]) + int(rec["kb"])
+                    for k in range(kb, kb + int(rec["count"])):
                         packed, u = int(T[k]["packed"]), float(T[k]["u"])
                         par = (bin(rep & packed & 0xFFFFFFFF).count("1") & 1) ^ parity(v & np.uint64(0xFF) & np.uint64((packed >> 32) & 0xFF))
                         word = (packed >> 48) & 0xFFFF                    # sign word: bit r = parity(r & zr)
@@ -358,7 +398,7 @@ def _plan_replay_matches_oracle(n, T, c, seed, weights, planner):
         assert np.all(B["n_views"] == 1) and not np.any(R["key"] == KEY_VIEW)
     elif weights is None and T >= 40 and c <= 3:
         # unstructured masks: further views turn most of the remaining records into pure-register records
-        assert np.any(B["n_views"] > 1) and np.sum(R["key"] < 32) < 0.25 * len(R)
+        assert np.any(B["n_views"] > 1) and 2 * np.sum(R["key"] == KEY_FUSED) > 0.5 * len(xm)       # most groups sit in fused view blocks
     if planner >= 2 and weights is None and T >= 30 and c <= 5:
         # unstructured masks: the register subspace is spanned by member masks, so some records need no partner read
         assert np.sum(R["key"] >= 32) >= len(B)

@@ -242,7 +242,8 @@ static int create_common(int n_qubits, int device, int rank, int world, const ch
         set((const void *)k_tile_expect<2, true, 1>, tile);
         set((const void *)k_tile_expect_db<3>, two_small);
         set((const void *)k_tile_apply, tile);
-        set((const void *)k_tile_expect_pipe, kPipeSmemBytes);
+        set((const void *)k_tile_expect_pipe<false>, kPipeSmemBytes);
+        set((const void *)k_tile_expect_pipe<true>, kPipeSmemBytes);
         set((const void *)k_sweep_small, tile);
         if (ea != cudaSuccess) return fail(std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(ea), B200VQE_ECUDA);
     }

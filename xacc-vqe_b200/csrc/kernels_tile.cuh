@@ -348,11 +348,7 @@ k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_byte
             const int n_r = sb.r_end - sb.r_begin;
             const int n_t = sb.t_end - sb.t_begin;
             const int4 *rsrc = reinterpret_cast<const int4 *>(recs + sb.r_begin);
-            for (int i = threadIdx.x; i < 2 * n_r; i += kBlock) {
-                int4 q = rsrc[i];
-                if (!(i & 1)) q.x -= sb.t_begin;
-                s_recs[i] = q;
-            }
+            for (int i = threadIdx.x; i < 2 * n_r; i += kBlock) s_recs[i] = rsrc[i];
             if (threadIdx.x == 0) s_recs[2 * n_r] = make_int4(0, 0, 0xff << 16, 0);
             const double2 *tsrc = reinterpret_cast<const double2 *>(terms) + sb.t_begin;
             for (int i = threadIdx.x; i < n_t; i += kBlock) s_terms[i] = tsrc[i];
@@ -483,11 +479,7 @@ k_tile_expect_db(const double2 *__restrict__ psi, int C, int M, unsigned chunk_b
             const int n_r = sb.r_end - sb.r_begin;
             const int n_t = sb.t_end - sb.t_begin;
             const int4 *rsrc = reinterpret_cast<const int4 *>(recs + sb.r_begin);
-            for (int i = threadIdx.x; i < 2 * n_r; i += kBlock) {
-                int4 q = rsrc[i];
-                if (!(i & 1)) q.x -= sb.t_begin;
-                s_recs[i] = q;
-            }
+            for (int i = threadIdx.x; i < 2 * n_r; i += kBlock) s_recs[i] = rsrc[i];
             if (threadIdx.x == 0) s_recs[2 * n_r] = make_int4(0, 0, 0xff << 16, 0);
             const double2 *tsrc = reinterpret_cast<const double2 *>(terms) + sb.t_begin;
             for (int i = threadIdx.x; i < n_t; i += kBlock) s_terms[i] = tsrc[i];
@@ -629,11 +621,7 @@ k_tile_apply(const double2 *__restrict__ src, double2 *__restrict__ dst, int C, 
         const int n_r = sb.r_end - sb.r_begin;
         const int n_t = sb.t_end - sb.t_begin;
         const int4 *rsrc = reinterpret_cast<const int4 *>(recs + sb.r_begin);
-        for (int i = threadIdx.x; i < 2 * n_r; i += kBlock) {
-            int4 q = rsrc[i];
-            if (!(i & 1)) q.x -= sb.t_begin;
-            s_recs[i] = q;
-        }
+        for (int i = threadIdx.x; i < 2 * n_r; i += kBlock) s_recs[i] = rsrc[i];
         if (threadIdx.x == 0) s_recs[2 * n_r] = make_int4(0, 0, 0xff << 16, 0);
         const double2 *tsrc = reinterpret_cast<const double2 *>(terms) + sb.t_begin;
         for (int i = threadIdx.x; i < n_t; i += kBlock) s_terms[i] = tsrc[i];

@@ -204,6 +204,37 @@ __device__ __forceinline__ int4 pipe_walk(const double2 (&a)[16], unsigned tile_
     return ra;
 }
 
+__device__ __forceinline__ double lds_f64(unsigned addr) {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+    return v;
+}
+
+// The fused block of a view (tile_plan.hpp, TileFusedSlot): the four generator groups of the view -- XR = 1, 2, 4, 8, one term
+// each, the first NE of them with even nY -- in one straight-line block: four independent chains of 8 pair products, the
+// signed butterfly and one POPC, no dispatch, no partner reads.  su: shared address of slot 0.
+template <int NE>
+__device__ __forceinline__ void fused_view(const double2 (&a)[16], unsigned su, unsigned v0, unsigned rep, double &acc) {
+    double part[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int4 q0 = lds_i4(su + 64u * j);                // zl, zt, u
+        const double2 s01 = lds_f64x2(su + 64u * j + 16u);
+        const double s2 = lds_f64(su + 64u * j + 48u);
+        double w[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int r = ((i >> j) << (j + 1)) | (i & ((1 << j) - 1));      // bit j clear
+            const double2 b = a[r | (1 << j)];
+            w[i] = j < NE ? fma(b.x, a[r].x, b.y * a[r].y) : fma(b.x, a[r].y, -(b.y * a[r].x));
+        }
+        const unsigned par = (unsigned)__popc((rep & (unsigned)q0.x) ^ (v0 & (unsigned)q0.y));
+        const double us = __hiloint2double(q0.w ^ (int)(par << 31), q0.z);
+        part[j] = us * signed_sum8(w, s01.x, s01.y, s2);
+    }
+    acc += (part[0] + part[1]) + (part[2] + part[3]);
+}
+
 struct PipeFillBatch {               // what a fill needs of its batch (shared memory, per group)
     uint32_t basis[kTileMaxDim];
     uint32_t seg[kTileMaxDim + 1];
@@ -213,6 +244,10 @@ struct PipeFillBatch {               // what a fill needs of its batch (shared m
 };
 constexpr int kPipeSmemBytes = kRingStages * kRingTileBytes + kRingGroups * (int)(sizeof(RingTables) + sizeof(PipeFillBatch)) + kRingGroups * kRingStages * 8 + 32 * 8;
 
+// WIDE = false: one register of at most 32 qubits (sel_mask = 0): a tile row is addressed by a 32-bit ELEMENT index
+// (high index << C | low bits) XORed with one of 16 per-batch row constants -- LOP3 + IMAD.WIDE + LDGSTS per row.
+// WIDE = true: pair registers of a sharded handle and registers above 32 qubits: 64-bit chunk arithmetic per row.
+template <bool WIDE>
 __global__ void __launch_bounds__(kRingThreads, 1)
 k_tile_expect_pipe(const double2 *__restrict__ psi, const double2 *__restrict__ psi_hi, unsigned sel_mask, int C, int M,
                    const TileBatch *__restrict__ batches, int n_batches,
@@ -280,15 +315,26 @@ k_tile_expect_pipe(const double2 *__restrict__ psi, const double2 *__restrict__ 
             f_rep = r0; f_dstep = d0;
         }
         const unsigned rb0 = fb.basis[M - 4], rb1 = fb.basis[M - 3], rb2 = fb.basis[M - 2], rb3 = fb.basis[M - 1];
-        const unsigned lm0 = fb.lam[0] << 4, lm1 = fb.lam[1] << 4, lm2 = fb.lam[2] << 4, lm3 = fb.lam[3] << 4;
         const unsigned base = f_rep ^ f_tc;
         const unsigned dst = tiles_u + (unsigned)fs * kRingTileBytes + (v0 << 4);
+        if constexpr (WIDE) {
+            const unsigned lm0 = fb.lam[0] << 4, lm1 = fb.lam[1] << 4, lm2 = fb.lam[2] << 4, lm3 = fb.lam[3] << 4;
 #pragma unroll
-        for (int r = 0; r < 16; ++r) {
-            const unsigned hi = base ^ ((r & 1) ? rb0 : 0u) ^ ((r & 2) ? rb1 : 0u) ^ ((r & 4) ? rb2 : 0u) ^ ((r & 8) ? rb3 : 0u);
-            const unsigned lor = lo_b ^ ((r & 1) ? lm0 : 0u) ^ ((r & 2) ? lm1 : 0u) ^ ((r & 4) ? lm2 : 0u) ^ ((r & 8) ? lm3 : 0u);
-            const char *slab = (hi & sel_mask) ? psi_h : psi_b;
-            cp_async16_u(dst + ((unsigned)r << 12), slab + (((unsigned long long)(hi & ~sel_mask) << chunk_shift) + lor));
+            for (int r = 0; r < 16; ++r) {
+                const unsigned hi = base ^ ((r & 1) ? rb0 : 0u) ^ ((r & 2) ? rb1 : 0u) ^ ((r & 4) ? rb2 : 0u) ^ ((r & 8) ? rb3 : 0u);
+                const unsigned lor = lo_b ^ ((r & 1) ? lm0 : 0u) ^ ((r & 2) ? lm1 : 0u) ^ ((r & 4) ? lm2 : 0u) ^ ((r & 8) ? lm3 : 0u);
+                const char *slab = (hi & sel_mask) ? psi_h : psi_b;
+                cp_async16_u(dst + ((unsigned)r << 12), slab + (((unsigned long long)(hi & ~sel_mask) << chunk_shift) + lor));
+            }
+        } else {
+            // element index of (this thread, register r):  e0 ^ (XOR of the row generators of the set bits of r)
+            const unsigned e0 = (base << C) | (lo_b >> 4);
+            const unsigned g0 = (rb0 << C) | fb.lam[0], g1 = (rb1 << C) | fb.lam[1], g2 = (rb2 << C) | fb.lam[2], g3 = (rb3 << C) | fb.lam[3];
+#pragma unroll
+            for (int r = 0; r < 16; ++r) {
+                const unsigned e = e0 ^ ((r & 1) ? g0 : 0u) ^ ((r & 2) ? g1 : 0u) ^ ((r & 4) ? g2 : 0u) ^ ((r & 8) ? g3 : 0u);
+                cp_async16_u(dst + ((unsigned)r << 12), psi + e);
+            }
         }
         cp_async_arrive_noinc(full_u + 8 * (kRingGroups * fs + (1 - g)));   // the item is walked by the other group
         // next item of this group's fill sequence: same batch -> masked add of the deposited stride
@@ -318,11 +364,7 @@ k_tile_expect_pipe(const double2 *__restrict__ psi, const double2 *__restrict__ 
             group_sync(g);
             const int n_r = tb.sb.r_end - tb.sb.r_begin, n_t = tb.sb.t_end - tb.sb.t_begin;
             const int4 *rsrc = reinterpret_cast<const int4 *>(recs + tb.sb.r_begin);
-            for (int k = (int)v0; k < 2 * n_r; k += kBlock) {
-                int4 q = rsrc[k];
-                if (!(k & 1)) q.x -= tb.sb.t_begin;
-                tb.recs[k] = q;
-            }
+            for (int k = (int)v0; k < 2 * n_r; k += kBlock) tb.recs[k] = rsrc[k];
             if (v0 == 0) tb.recs[2 * n_r] = make_int4(0, 0, kTileRecKeyEnd << 16, 0);
             const double2 *tsrc = reinterpret_cast<const double2 *>(terms) + tb.sb.t_begin;
             for (int k = (int)v0; k < n_t; k += kBlock) tb.terms[k] = tsrc[k];
@@ -343,7 +385,11 @@ k_tile_expect_pipe(const double2 *__restrict__ psi, const double2 *__restrict__ 
         mbar_wait(full_u + 8 * (kRingGroups * s + g), u & 1u);     // the tile has landed (all 256 copying threads' cp.async are complete)
         const unsigned tile_u = tiles_u + (unsigned)s * kRingTileBytes;
         {
-            unsigned ru = recs_u, view = 0;
+            unsigned ru = recs_u, view = 0, pat = 0;
+            {   // plans with fused view blocks open every view, view 0 included, with a marker
+                const int4 m = lds_i4(ru);
+                if (((unsigned)m.z >> 16) == (unsigned)kTileRecKeyView) { view = (unsigned)m.w; pat = (unsigned)m.y; ru += 32; }
+            }
 #pragma unroll 1
             for (;;) {
                 // registers of this view: 16 amplitudes of the tile at  base ^ (XOR of the view's register columns)
@@ -354,9 +400,20 @@ k_tile_expect_pipe(const double2 *__restrict__ psi, const double2 *__restrict__ 
 #pragma unroll
                 for (int r = 0; r < 16; ++r)
                     a[r] = lds_f64x2(tile_u + (base ^ ((r & 1) ? g0 : 0u) ^ ((r & 2) ? g1 : 0u) ^ ((r & 4) ? g2 : 0u) ^ ((r & 8) ? g3 : 0u)));
+                if (pat) {                                  // the view's four generator groups, fused (pat - 1 of them with even nY)
+                    switch (pat) {
+                        case 1: fused_view<0>(a, ru, v0, rep, acc); break;
+                        case 2: fused_view<1>(a, ru, v0, rep, acc); break;
+                        case 3: fused_view<2>(a, ru, v0, rep, acc); break;
+                        case 4: fused_view<3>(a, ru, v0, rep, acc); break;
+                        default: fused_view<4>(a, ru, v0, rep, acc); break;
+                    }
+                    ru += 4u * (unsigned)sizeof(TileFusedSlot);
+                }
                 const int4 stop = pipe_walk(a, tile_u, v0, rep, ru, terms_u, acc);
                 if (((unsigned)stop.z >> 16) != (unsigned)kTileRecKeyView) break;
                 view = (unsigned)stop.w;                    // marker: the records that follow want the registers of this view
+                pat = (unsigned)stop.y;
                 ru += 32;
             }
         }

@@ -24,6 +24,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
+#include <cstring>
 #include <unordered_map>
 #include <vector>
 
@@ -81,7 +82,7 @@ static_assert(sizeof(TileTerm) == 16, "TileTerm layout");
 // Records of a batch are sorted by key, so the device runs one straight-line, fully specialised loop per key:
 //   key = which * 16 + (xr ? xr - 1 : 15),  xr = xv >> 8 (register bits of the virtual flip mask), which = 0 even nY / 1 odd nY
 struct TileRec {                     // 32 bytes
-    uint32_t kb;                     // first term (relative to the batch's t_begin once staged)
+    uint32_t kb;                     // first term, relative to the batch's t_begin
     uint32_t count;                  // terms of this record (>= 1)
     uint16_t xv;
     uint8_t key;
@@ -93,8 +94,29 @@ struct TileRec {                     // 32 bytes
 };
 static_assert(sizeof(TileRec) == 32, "TileRec layout");
 
+// One slot of a FUSED VIEW BLOCK (64 bytes = two entries of the record stream).  The four register bits of a view are the flip
+// masks of four member groups ("generators": XR = 1, 2, 4, 8); when those groups have one term each, the pipelined kernel
+// evaluates the four of them in one straight-line block right after loading the view's registers -- no per-record dispatch,
+// four independent dependency chains -- from these slots.  Slot j: XR = 1 << j, pairs {r, r | 1 << j}; the first NE slots of a
+// block hold even-nY terms (Re w), the others odd-nY terms (Im w) or nothing (u = 0).
+struct TileFusedSlot {
+    uint32_t zl;                     // z on the high index bits
+    uint32_t zt;                     // thread bits of z in the view's coordinates
+    double u;                        // 2 * coefficient; 0: empty slot
+    double s0, s1;                   // +-1.0: (-1)^{z bit} of the three register bits other than j, in ascending order (s2 below)
+    uint32_t kb;                     // second half, laid out like a TileRec: the plan term (relative to the batch's t_begin),
+    uint32_t pad;
+    uint16_t xv; uint8_t key; uint8_t pad0;      // key = kTileRecKeyFused
+    uint32_t view;
+    double s2;
+    uint64_t pad2;
+};
+static_assert(sizeof(TileFusedSlot) == 2 * sizeof(TileRec), "TileFusedSlot layout");
+
 constexpr int kTileRecKeys = 32;      // (which, XR) combinations; + 32: pure-register records (expectation engine)
-constexpr int kTileRecKeyView = 0xfe; // marker record between the records of two views
+constexpr int kTileRecKeyFused = 0xfd; // the entries of a fused view block (never dispatched: the block is skipped as a whole)
+constexpr int kTileRecKeyView = 0xfe; // marker record in front of the records of a view: TileRec::view = the view; count = 0: no fused block,
+                                      // 1 + NE: a fused block of 4 TileFusedSlot follows, its first NE slots hold even-nY terms
 constexpr int kTileRecKeyEnd = 0xff;  // sentinel the kernels append after the last record of a batch
 constexpr int kStageRecs = 128;      // records / terms of one batch staged in shared memory by k_tile_expect (+ kTileMaxViews markers);
 constexpr int kStageTerms = 256;     // expectation plans are built with these as per-batch capacities
@@ -111,6 +133,7 @@ struct TilePlan {
     std::vector<TileRec> recs;       // expectation engine only (build_tile_records)
     std::vector<uint8_t> group_view; // per group: the view its xv / its terms' z parts are expressed in (all 0 without views)
     int max_views = 1;               // largest TileBatch::n_views of the plan
+    bool fused = false;              // the record stream has view markers in front of EVERY view and fused view blocks
 };
 
 // Which tiles (cosets) of every batch a rank of a sharded register evaluates in <psi|H|psi>: a contiguous 1/world share;
@@ -363,6 +386,11 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
         std::vector<uint32_t> lo(NM);
         for (size_t k = 0; k < NM; ++k) { cc[k] = rr.coords(gs[members[k]].x >> C); lo[k] = (uint32_t)(gs[members[k]].x & lomask); }
 
+        // 0: one even-nY term, 1: one odd-nY term, 2: anything else
+        auto fuse_type = [&](int k) {
+            const G &g = gs[members[k]];
+            return g.te - g.tb == 1 ? (in[order[g.tb]].odd ? 1 : 0) : 2;
+        };
         // ---- virtual coordinates: newb[i] (in rr coordinates) <-> virtual bit C + i; the top RB are the register bits ----
         std::vector<uint64_t> newb;
         uint32_t lam[4] = {0, 0, 0, 0};
@@ -396,6 +424,7 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
             for (size_t k = 0; k < NM; ++k) V[k] = (cc[k] << C) | lo[k];
             Rref rc, rv;
             std::vector<uint64_t> rho;
+            std::vector<int> picked;
             for (int pick = 0; pick < RB; ++pick) {
                 int best = -1, best_score = -1;
                 for (size_t k = 0; k < NM; ++k) {
@@ -409,9 +438,12 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
                 if (best < 0) break;
                 rv.insert(V[best]);
                 rc.insert(cc[best]);
-                lam[rho.size()] = lo[best];
-                rho.push_back(cc[best]);
+                picked.push_back(best);
             }
+            // register bit j <-> j-th generator: single-term even-nY groups first, then single-term odd-nY, then the rest
+            // (the fused view body of the pipelined kernel, build_tile_records)
+            std::stable_sort(picked.begin(), picked.end(), [&](int a, int b) { return fuse_type(a) < fuse_type(b); });
+            for (int k : picked) { lam[rho.size()] = lo[k]; rho.push_back(cc[k]); }
             for (int i = 0; i < dim && (int)rho.size() < RB; ++i)
                 if (rc.reduce(1ull << i)) { rc.insert(1ull << i); rho.push_back(1ull << i); }
             std::vector<uint64_t> theta;
@@ -491,6 +523,7 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
             while ((int)views.size() < std::min(o.views, kTileMaxViews)) {
                 Rref rc, rv;
                 std::vector<uint64_t> reg_u;
+                std::vector<int> picked;
                 for (int pick = 0; pick < RB; ++pick) {
                     int best = -1, best_score = -1;
                     for (size_t k = 0; k < NM; ++k) {
@@ -504,8 +537,10 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
                     if (best < 0) break;
                     rv.insert(Vu[best]);
                     rc.insert(cc[best]);
-                    reg_u.push_back(Vu[best]);
+                    picked.push_back(best);
                 }
+                std::stable_sort(picked.begin(), picked.end(), [&](int a, int b) { return fuse_type(a) < fuse_type(b); });
+                for (int k : picked) reg_u.push_back(Vu[k]);
                 int gain = 0;
                 for (size_t m = 0; m < NM; ++m) if (open[m] && !rv.reduce(Vu[m])) gain += wgt[m];
                 if (reg_u.empty() || gain < kViewMinGain) break;
@@ -626,42 +661,103 @@ inline TilePlanOpts apply_plan_opts(int planner = 2) {
 // Records of the tile kernels for a plan built with the kStage* capacities.  allow_pure (expectation plans built with
 // shear): a record whose sheared flip mask has no thread part gets key + 32 -- the kernel then takes the partner from
 // the thread's own registers.
-inline void build_tile_records(TilePlan &P, bool allow_pure = false) {
+inline void build_tile_records(TilePlan &P, bool allow_pure = false, bool fuse = false) {
     P.recs.clear();
+    P.fused = fuse;
+    constexpr unsigned tmask = (1u << kTileThreadBits) - 1;
     for (TileBatch &B : P.batches) {
+        // fused view blocks: per view, the generator groups (xv = register bit j alone, one term)
+        struct Block { int slot_group[4]; int ne; bool on; };
+        std::vector<Block> blocks(fuse ? B.n_views : 0u);
+        std::vector<char> in_block(B.g_end - B.g_begin, 0);
+        for (size_t v = 0; v < blocks.size(); ++v) {
+            Block &bl = blocks[v];
+            int type[4];
+            for (int j = 0; j < 4; ++j) { bl.slot_group[j] = -1; type[j] = 2; }
+            for (int g = B.g_begin; g < B.g_end; ++g) {
+                const TileGroup &tg = P.groups[g];
+                if (P.group_view[g] != v || (tg.xv & tmask) || tg.n_even + tg.n_odd != 1) continue;
+                const unsigned xr = tg.xv >> kTileThreadBits;
+                if (xr == 0 || (xr & (xr - 1))) continue;
+                const int j = 31 - __builtin_clz(xr);
+                bl.slot_group[j] = g;
+                type[j] = tg.n_even ? 0 : 1;
+            }
+            // the planner orders the generators even, odd, rest; a slot that breaks the order stays a plain record
+            int n_used = 0;
+            bl.ne = 0;
+            for (int j = 0, prev = 0; j < 4; ++j) {
+                if (type[j] < prev || type[j] == 2) { bl.slot_group[j] = -1; prev = 2; continue; }
+                prev = type[j];
+                ++n_used;
+                if (type[j] == 0) bl.ne = j + 1;
+            }
+            bl.on = n_used >= 2;
+            if (bl.on) for (int j = 0; j < 4; ++j) if (bl.slot_group[j] >= 0) in_block[bl.slot_group[j] - B.g_begin] = 1;
+        }
         std::vector<TileRec> rs;
         for (int g = B.g_begin; g < B.g_end; ++g) {
+            if (in_block[g - B.g_begin]) continue;
             const TileGroup &tg = P.groups[g];
             const unsigned xr = tg.xv >> kTileThreadBits;
             const uint32_t view = (size_t)g < P.group_view.size() ? P.group_view[g] : 0u;
-            const bool pure = (allow_pure || view) && (tg.xv & ((1u << kTileThreadBits) - 1)) == 0;
+            const bool pure = (allow_pure || view) && (tg.xv & tmask) == 0;
             for (int which = 0; which < 2; ++which) {
                 const uint32_t cnt = which ? tg.n_odd : tg.n_even;
                 if (!cnt) continue;
                 TileRec r{};
-                r.kb = tg.kb + (which ? tg.n_even : 0);
+                const uint32_t kb = tg.kb + (which ? tg.n_even : 0);
+                r.kb = kb - (uint32_t)B.t_begin;
                 r.count = cnt;
                 r.xv = tg.xv;
                 r.key = (uint8_t)((pure ? 32 : 0) + which * 16 + (xr ? xr - 1 : 15));
                 r.view = view;
-                r.packed0 = P.terms[r.kb].packed;
-                r.u0 = P.terms[r.kb].u;
+                r.packed0 = P.terms[kb].packed;
+                r.u0 = P.terms[kb].u;
                 rs.push_back(r);
             }
         }
         std::stable_sort(rs.begin(), rs.end(), [](const TileRec &a, const TileRec &b) { return a.view != b.view ? a.view < b.view : a.key < b.key; });
         B.r_begin = (int32_t)P.recs.size();
-        uint32_t cur_view = 0;
-        for (const TileRec &r : rs) {
-            if (r.view != cur_view) {          // marker: the kernel reloads its registers in the layout of view r.view
-                TileRec m{};
-                m.key = (uint8_t)kTileRecKeyView;
-                m.view = r.view;
-                P.recs.push_back(m);
-                cur_view = r.view;
+        auto open_view = [&](uint32_t v) {      // marker (+ fused block): the kernel loads its registers in the layout of view v
+            TileRec m{};
+            m.key = (uint8_t)kTileRecKeyView;
+            m.view = v;
+            const bool on = fuse && blocks[v].on;
+            m.count = on ? 1u + (uint32_t)blocks[v].ne : 0u;
+            P.recs.push_back(m);
+            if (!on) return;
+            for (int j = 0; j < 4; ++j) {
+                TileFusedSlot fs{};
+                fs.key = (uint8_t)kTileRecKeyFused;
+                fs.view = v;
+                fs.s0 = fs.s1 = fs.s2 = 1.0;
+                const int g = blocks[v].slot_group[j];
+                if (g >= 0) {
+                    const TileTerm &tt = P.terms[P.groups[g].kb];
+                    fs.zl = (uint32_t)tt.packed;
+                    fs.zt = (uint32_t)(tt.packed >> 32) & 0xffu;
+                    fs.u = tt.u;
+                    fs.kb = P.groups[g].kb - (uint32_t)B.t_begin;
+                    fs.xv = P.groups[g].xv;
+                    const unsigned zr = (unsigned)(tt.packed >> 40) & 0xfu;
+                    double *sg[3] = {&fs.s0, &fs.s1, &fs.s2};
+                    for (int k = 0; k < 3; ++k) if ((zr >> (k < j ? k : k + 1)) & 1u) *sg[k] = -1.0;
+                }
+                TileRec half[2];
+                memcpy(half, &fs, sizeof(fs));
+                P.recs.push_back(half[0]);
+                P.recs.push_back(half[1]);
             }
+        };
+        uint32_t cur_view = 0;
+        if (fuse) open_view(0);
+        for (const TileRec &r : rs) {
+            if (fuse) while (cur_view < r.view) open_view(++cur_view);
+            else if (r.view != cur_view) { open_view(r.view); cur_view = r.view; }
             P.recs.push_back(r);
         }
+        if (fuse) while (cur_view + 1 < B.n_views) open_view(++cur_view);     // views whose groups all sit in their fused block
         B.r_end = (int32_t)P.recs.size();
     }
 }
