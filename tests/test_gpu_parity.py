@@ -158,9 +158,10 @@ def test_tile_apply_matches_streaming_kernel_and_oracle(xb, n, T, seed, cbits):
     ref = co.apply(n, xm, zm, cf, psi)
     scale = np.abs(cf).sum()
     outs = {}
-    for engine in ("tile", "stream"):
+    for engine in ("tile", "tile-classic", "stream"):
         be = xb.Backend(n)
-        be.set_option("apply-engine", engine)
+        be.set_option("apply-engine", engine.split("-")[0])
+        be.set_option("apply-kernel", "classic" if engine == "tile-classic" else "pipe")     # k_tile_apply | k_tile_apply_pipe
         be.set_option("tile-chunk-bits", cbits)
         be.n_slots(2)
         be.set_hamiltonian(xm, zm, cf)
@@ -172,6 +173,25 @@ def test_tile_apply_matches_streaming_kernel_and_oracle(xb, n, T, seed, cbits):
         assert abs(alpha - np.vdot(psi, ref)) < REL * scale, engine
         be.close()
     assert np.abs(outs["tile"] - outs["stream"]).max() < 1e-12 * scale
+    assert np.abs(outs["tile"] - outs["tile-classic"]).max() < 1e-12 * scale
+
+
+@pytest.mark.parametrize("kernel", ["pipe", "classic"])
+@pytest.mark.parametrize("n,T,seed", [(14, 60, 7), (17, 200, 8)])
+def test_lanczos_on_the_tile_engine(xb, n, T, seed, kernel):
+    """Lanczos with H psi on the tile engine: the pipelined kernel leaves alpha_j = <v_j|H v_j> in its last batch (no k_alpha
+    pass), the classic one runs k_alpha; both against ARPACK on the oracle's operator, and against each other step for step."""
+    xm, zm, cf = random_hamiltonian(n, T, seed)
+    be = xb.Backend(n)
+    be.set_option("apply-engine", "tile")
+    be.set_option("apply-kernel", kernel)
+    be.set_hamiltonian(xm, zm, cf)
+    e0, it, res = be.lanczos_ground(tol=1e-11, max_iter=3000, want_vector=True, seed=seed)
+    want, _ = po.ground_state_eigsh(xm, zm, cf, n, tol=1e-13, apply=lambda v: co.apply(n, xm, zm, cf, v))
+    assert rel(e0, want) < REL
+    vec = be.download(0)
+    assert np.linalg.norm(co.apply(n, xm, zm, cf, vec) - e0 * vec) < 1e-7 * np.abs(cf).sum()
+    be.close()
 
 
 def test_complex_coefficients(xb):
