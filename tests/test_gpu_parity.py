@@ -158,10 +158,11 @@ def test_tile_apply_matches_streaming_kernel_and_oracle(xb, n, T, seed, cbits):
     ref = co.apply(n, xm, zm, cf, psi)
     scale = np.abs(cf).sum()
     outs = {}
-    for engine in ("tile", "tile-classic", "stream"):
+    for engine in ("tile", "tile-classic", "tile-pipe", "stream"):
         be = xb.Backend(n)
         be.set_option("apply-engine", engine.split("-")[0])
-        be.set_option("apply-kernel", "classic" if engine == "tile-classic" else "pipe")     # k_tile_apply | k_tile_apply_pipe
+        # k_tile_apply_pipe8 (default) | k_tile_apply | k_tile_apply_pipe
+        be.set_option("apply-kernel", engine.split("-")[1] if "-" in engine else "auto")
         be.set_option("tile-chunk-bits", cbits)
         be.n_slots(2)
         be.set_hamiltonian(xm, zm, cf)
@@ -174,9 +175,10 @@ def test_tile_apply_matches_streaming_kernel_and_oracle(xb, n, T, seed, cbits):
         be.close()
     assert np.abs(outs["tile"] - outs["stream"]).max() < 1e-12 * scale
     assert np.abs(outs["tile"] - outs["tile-classic"]).max() < 1e-12 * scale
+    assert np.abs(outs["tile"] - outs["tile-pipe"]).max() < 1e-12 * scale
 
 
-@pytest.mark.parametrize("kernel", ["pipe", "classic"])
+@pytest.mark.parametrize("kernel", ["pipe8", "pipe", "classic"])
 @pytest.mark.parametrize("n,T,seed", [(14, 60, 7), (17, 200, 8)])
 def test_lanczos_on_the_tile_engine(xb, n, T, seed, kernel):
     """Lanczos with H psi on the tile engine: the pipelined kernel leaves alpha_j = <v_j|H v_j> in its last batch (no k_alpha

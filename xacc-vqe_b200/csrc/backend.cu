@@ -245,6 +245,8 @@ static int create_common(int n_qubits, int device, int rank, int world, const ch
         set((const void *)k_tile_apply, tile);
         set((const void *)k_tile_apply_pipe<false>, kApplyPipeSmemBytes);
         set((const void *)k_tile_apply_pipe<true>, kApplyPipeSmemBytes);
+        set((const void *)k_tile_apply_pipe8<false>, kApply8SmemBytes);
+        set((const void *)k_tile_apply_pipe8<true>, kApply8SmemBytes);
         set((const void *)k_tile_expect_pipe<false>, kPipeSmemBytes);
         set((const void *)k_tile_expect_pipe<true>, kPipeSmemBytes);
         set((const void *)k_sweep_small, tile);
@@ -341,9 +343,10 @@ int b200vqe_set_option(b200vqe_handle h, const char *key, const char *value) {
         return 0;
     }
     if (k == "apply-kernel") {
-        if (v == "auto" || v == "pipe") h->opt_apply_kernel = 0;
+        if (v == "auto" || v == "pipe8") h->opt_apply_kernel = 0;
         else if (v == "classic") h->opt_apply_kernel = 1;
-        else FAIL(B200VQE_EINVAL, "apply-kernel must be auto, pipe or classic");
+        else if (v == "pipe") h->opt_apply_kernel = 2;
+        else FAIL(B200VQE_EINVAL, "apply-kernel must be auto, pipe8, pipe or classic");
         return 0;
     }
     if (k == "apply-engine") {

@@ -540,14 +540,15 @@ __device__ __forceinline__ void apply_rec_body(double2 (&acc)[16], const double2
         const double u = __hiloint2double(rb.w, rb.z);
 #pragma unroll
         for (int r = 0; r < 16; ++r) {
-            const double2 b = P[(r ^ XR) << 8];
-            const double f = flip_bit(u, S, r);
+            double2 b = P[(r ^ XR) << 8];
+            b.x = flip_bit(b.x, S, r);           // the sign rides on the partner amplitude: two LOP3 on the words just loaded
+            b.y = flip_bit(b.y, S, r);
             if (WHICH == 0) {            // even nY: real factor
-                acc[r].x = fma(f, b.x, acc[r].x);
-                acc[r].y = fma(f, b.y, acc[r].y);
-            } else {                     // odd nY: factor i * f
-                acc[r].x = fma(-f, b.y, acc[r].x);
-                acc[r].y = fma(f, b.x, acc[r].y);
+                acc[r].x = fma(u, b.x, acc[r].x);
+                acc[r].y = fma(u, b.y, acc[r].y);
+            } else {                     // odd nY: factor i * u
+                acc[r].x = fma(-u, b.y, acc[r].x);
+                acc[r].y = fma(u, b.x, acc[r].y);
             }
         }
         return;
