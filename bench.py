@@ -304,7 +304,6 @@ def run_gpu(args):
     be.set_option("tile-planner", args.planner)
     be.set_option("tile-dispatch", args.dispatch)
     be.set_option("expect-kernel", args.expect_kernel)
-    be.set_option("apply-kernel", args.apply_kernel)
     t0 = time.perf_counter()
     be.set_hamiltonian(xm, zm, cf)
     set_ham_ms = (time.perf_counter() - t0) * 1e3
@@ -615,7 +614,6 @@ def main():
     ap.add_argument("--tile-ctas", type=int, default=2, choices=[2, 3], help="tile engine: resident CTAs per SM")
     ap.add_argument("--tile-bits", type=int, default=12, choices=[11, 12], help="tile engine: 12 = 4096-amplitude tiles, 11 = 2048 double-buffered")
     ap.add_argument("--expect-kernel", default="auto", choices=["auto", "pipe", "classic"])
-    ap.add_argument("--apply-kernel", default="auto", choices=["auto", "pipe8", "pipe", "classic"], help="tile H psi kernel")
     ap.add_argument("--dispatch", type=int, default=1, choices=[0, 1, 2, 3])
     ap.add_argument("--planner", type=int, default=3, choices=[1, 2, 3], help="tile planner version (csrc/tile_plan.hpp)")
     ap.add_argument("--chunk-bits", type=int, default=3, help="tile engine: log2 contiguous amplitudes per HBM chunk")

@@ -278,8 +278,8 @@ def replay_apply(n, c, B, R, T, classes, psi, rank=0, world=1):
                 acc = np.zeros(1 << TILE_BITS, complex)
                 for rec in recs:
                     key, xv = int(rec["key"]), int(rec["xv"])
-                    which, xr = key >> 4, ((key & 15) + 1) & 15
-                    assert xr == xv >> 8 and key < 32 and not np.any(b["lam"])      # H psi plans: no shear, no pure records
+                    which, xr = key >> 3, xv >> 8              # H psi records: key = which * 8 + (XR & 7), XR bit 3 is read from xv
+                    assert key < 16 and (key & 7) == (xr & 7) and not np.any(b["lam"]) and b["n_views"] == 1      # no shear, no views
                     f = np.zeros(1 << TILE_BITS)
                     kb = int(b["t_begin"]) + int(rec["kb"])
                     for k in range(kb, kb + int(rec["count"])):

@@ -242,9 +242,6 @@ static int create_common(int n_qubits, int device, int rank, int world, const ch
         set((const void *)k_tile_expect<3, false, 1>, tile);
         set((const void *)k_tile_expect<2, true, 1>, tile);
         set((const void *)k_tile_expect_db<3>, two_small);
-        set((const void *)k_tile_apply, tile);
-        set((const void *)k_tile_apply_pipe<false>, kApplyPipeSmemBytes);
-        set((const void *)k_tile_apply_pipe<true>, kApplyPipeSmemBytes);
         set((const void *)k_tile_apply_pipe8<false>, kApply8SmemBytes);
         set((const void *)k_tile_apply_pipe8<true>, kApply8SmemBytes);
         set((const void *)k_tile_expect_pipe<false>, kPipeSmemBytes);
@@ -340,13 +337,6 @@ int b200vqe_set_option(b200vqe_handle h, const char *key, const char *value) {
         else if (v == "tile") h->opt_expect_engine = 1;
         else if (v == "stream") h->opt_expect_engine = 2;
         else FAIL(B200VQE_EINVAL, "expect-engine must be auto, tile or stream");
-        return 0;
-    }
-    if (k == "apply-kernel") {
-        if (v == "auto" || v == "pipe8") h->opt_apply_kernel = 0;
-        else if (v == "classic") h->opt_apply_kernel = 1;
-        else if (v == "pipe") h->opt_apply_kernel = 2;
-        else FAIL(B200VQE_EINVAL, "apply-kernel must be auto, pipe8, pipe or classic");
         return 0;
     }
     if (k == "apply-engine") {

@@ -119,7 +119,6 @@ struct b200vqe_ctx {
     int opt_tile_bits = 12;             // tile of the <psi|H|psi> engine: 12 = 4096 amplitudes single-buffered, 11 = 2048 double-buffered
     int opt_shard_exchange = 0;         // tile H psi on a sharded register: 0 all-gather (auto), 1 pairwise pipeline, 2 needed slabs only (one send/recv group)
     int opt_expect_kernel = 0;          // <psi|H|psi> on 4096-amplitude tiles: 0 pipelined kernel (k_tile_expect_pipe: 3-stage cp.async ring), 1 k_tile_expect
-    int opt_apply_kernel = 0;           // tile H psi: 0 k_tile_apply_pipe8 (pipelined, 512 threads per tile; shards up to 32 local qubits), 1 k_tile_apply, 2 k_tile_apply_pipe (256 threads per tile)
     int opt_tile_dispatch = 1;          // record dispatch of k_tile_expect: 0 key-test chain, 1 jump table per record, 2 chain without pure-register records
     int opt_tile_planner = 3;           // tile planner version (tile_plan.hpp: 3 = 2 + several register subspaces (views) per batch, 2 = collision-greedy subspaces + sheared register subspace, 1 = first version)
     int opt_tile_chunk_bits = 3;        // C: contiguous amplitudes per chunk = 2^C (128 B at C = 3)

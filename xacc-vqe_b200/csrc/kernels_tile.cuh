@@ -8,10 +8,10 @@
 //     E += u s(j) Re w  |  u s(j) Im w,   w = conj(psi[j^x]) psi[j],
 // where the sign of a term at register r factorises into a thread constant (one POPC over the coset part xor the
 // thread part) and a Walsh function of r: one 8-point signed butterfly (7 DFMA) per term on top of the record's
-// Re w / Im w products.  H psi keeps 16 complex accumulators per thread and reads all 16 partner rows per record.
+// Re w / Im w products.
 //
 // Kernels: k_tile_expect<MINB, PT> (single buffer; PT = per-term sums instead of the energy), k_tile_expect_db<3>
-// (2048-amplitude tiles, cp.async double buffering, opt-in), k_tile_apply (one launch per batch), k_sum_term_partials.
+// (2048-amplitude tiles, cp.async double buffering, opt-in), k_sum_term_partials; H psi: kernels_tile_apply_pipe.cuh.
 // HBM traffic of <psi|H|psi>: 16 B per amplitude per BATCH (>= kTileBits - C groups), no writes.
 #pragma once
 #include "kernels.cuh"
@@ -513,181 +513,6 @@ k_tile_expect_db(const double2 *__restrict__ psi, int C, int M, unsigned chunk_b
     cp_async_wait_all();
     double v[1] = {acc};
     grid_reduce<1>(v, partials, counter, out, 1.0);
-}
-
-// ---------------------------------------------------------------------------------------------
-// K2 on the tile engine:  dst (+)= in_scale * sum_{groups of ONE batch} f_g(j ^ x_g) src[j ^ x_g]
-//
-// One launch per batch (stream order makes batch b's read-modify-write of dst see batch b-1's).  The tile of src is
-// staged in shared memory exactly as in k_tile_expect; a thread keeps 16 complex accumulators for its own 16 outputs,
-// walks every group of the batch (16 conflict-free LDS.128 per group), and adds the tile's contribution to dst once.
-// HBM traffic per batch: 16 B (src) + 32 B (dst read + write) per amplitude instead of 16 B per GROUP.
-// Signs are evaluated at the thread's own index j (s(j ^ x) = s(j) (-1)^nY is folded into the coefficient on the
-// host): u = coef for even nY, -Im(coef) for odd nY.
-//   first != 0:  dst = in_scale * acc - prev_scale * dst   (prev_scale = 0 unless fuse_prev)   [Lanczos: w' = H v_j - beta_j v_{j-1}]
-//   first == 0:  dst += in_scale * acc
-// ---------------------------------------------------------------------------------------------
-// one record on the 16 outputs of a thread: partner of register r is row r ^ XR of thread v0 ^ xt (immediate offsets)
-template <int WHICH, int XR>
-__device__ __forceinline__ void apply_rec_body(double2 (&acc)[16], const double2 *__restrict__ P, unsigned v0, unsigned rep,
-                                               const int4 ra, const int4 rb, const double2 *__restrict__ s_terms) {
-    const int count = ra.y;
-    if (count == 1) {
-        // single term (every group of an unstructured Hamiltonian): the factor at register r is +-u
-        const unsigned zl = (unsigned)rb.x, hw = (unsigned)rb.y;
-        const unsigned par = (unsigned)__popc((rep & zl) ^ (v0 & hw & 0xffu)) & 1u;
-        const unsigned S = (hw >> 16) ^ (0u - par);            // bit r: sign of the term at register r
-        const double u = __hiloint2double(rb.w, rb.z);
-#pragma unroll
-        for (int r = 0; r < 16; ++r) {
-            double2 b = P[(r ^ XR) << 8];
-            b.x = flip_bit(b.x, S, r);           // the sign rides on the partner amplitude: two LOP3 on the words just loaded
-            b.y = flip_bit(b.y, S, r);
-            if (WHICH == 0) {            // even nY: real factor
-                acc[r].x = fma(u, b.x, acc[r].x);
-                acc[r].y = fma(u, b.y, acc[r].y);
-            } else {                     // odd nY: factor i * u
-                acc[r].x = fma(-u, b.y, acc[r].x);
-                acc[r].y = fma(u, b.x, acc[r].y);
-            }
-        }
-        return;
-    }
-    const double2 *tp = s_terms + ra.x;
-#pragma unroll
-    for (int part = 0; part < 4; ++part) {       // four registers at a time keeps the factor sums in registers
-        double f[4] = {0.0, 0.0, 0.0, 0.0};
-        double2 t = tp[0];
-#pragma unroll 1
-        for (int e = 0; e < count; ++e) {
-            const unsigned long long packed = (unsigned long long)__double_as_longlong(t.x);
-            const double u = t.y;
-            if (e + 1 < count) t = tp[e + 1];
-            const unsigned zl = (unsigned)packed, hw = (unsigned)(packed >> 32);
-            const unsigned par = (unsigned)__popc((rep & zl) ^ (v0 & hw & 0xffu)) & 1u;
-            const unsigned S = (hw >> 16) ^ (0u - par);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) f[i] += flip_bit(u, S, part * 4 + i);
-        }
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int r = part * 4 + i;
-            const double2 b = P[(r ^ XR) << 8];
-            if (WHICH == 0) {
-                acc[r].x = fma(f[i], b.x, acc[r].x);
-                acc[r].y = fma(f[i], b.y, acc[r].y);
-            } else {
-                acc[r].x = fma(-f[i], b.y, acc[r].x);
-                acc[r].y = fma(f[i], b.x, acc[r].y);
-            }
-        }
-    }
-}
-
-template <int K>
-__device__ __forceinline__ void apply_runs(double2 (&acc)[16], const double2 *__restrict__ tile, unsigned v0, unsigned rep,
-                                           const int4 *__restrict__ s_recs, const double2 *__restrict__ s_terms, int &gi, int4 &ra,
-                                           int4 &rb) {
-    if constexpr (K < kTileRecKeys) {
-        while (((unsigned)ra.z >> 16) == (unsigned)K) {
-            const int4 ca = ra, cb = rb;
-            ++gi;
-            ra = s_recs[2 * gi];
-            rb = s_recs[2 * gi + 1];
-            apply_rec_body<(K >> 4), (((K & 15) + 1) & 15)>(acc, tile + ((v0 ^ (unsigned)ca.z) & 0xffu), v0, rep, ca, cb, s_terms);
-        }
-        apply_runs<K + 1>(acc, tile, v0, rep, s_recs, s_terms, gi, ra, rb);
-    }
-}
-
-__global__ void __launch_bounds__(kBlock, 2)
-k_tile_apply(const double2 *__restrict__ src, double2 *__restrict__ dst, int C, int M, unsigned chunk_bytes,
-             const TileBatch *__restrict__ batch, unsigned tile_count, const TileRec *__restrict__ recs,
-             const TileTerm *__restrict__ terms, int first, const double *norm_src, const double *norm_prev, int fuse_prev) {
-    extern __shared__ __align__(16) unsigned char tile_raw[];
-    double2 *tile = reinterpret_cast<double2 *>(tile_raw);
-    __shared__ TileBatch sb;
-    __shared__ __align__(16) int4 s_recs[2 * (kStageRecs + 1)];
-    __shared__ __align__(16) double2 s_terms[kStageTerms];
-    const unsigned v0 = threadIdx.x;
-    const unsigned lo = v0 & ((1u << C) - 1u);
-    if (threadIdx.x < kTileBatchWords) reinterpret_cast<uint32_t *>(&sb)[threadIdx.x] = reinterpret_cast<const uint32_t *>(batch)[threadIdx.x];
-    __syncthreads();
-    unsigned Tc = 0;
-    for (int i = 0; i < 8 - C; ++i) if ((v0 >> (C + i)) & 1u) Tc ^= sb.basis[i];
-    const unsigned rb0 = sb.basis[M - 4], rb1 = sb.basis[M - 3], rb2 = sb.basis[M - 2], rb3 = sb.basis[M - 1];
-    // the 8 lanes sharing a 128-byte line split its 16 rows between them: this thread prefetches rows 2(lane & 7), +1
-    const unsigned pcA = Tc ^ ((v0 & 1u) ? rb1 : 0u) ^ ((v0 & 2u) ? rb2 : 0u) ^ ((v0 & 4u) ? rb3 : 0u);
-    {   // stage the batch's records (+ sentinel) and terms; the planner keeps every batch within kStageRecs / kStageTerms
-        const int n_r = sb.r_end - sb.r_begin;
-        const int n_t = sb.t_end - sb.t_begin;
-        const int4 *rsrc = reinterpret_cast<const int4 *>(recs + sb.r_begin);
-        for (int i = threadIdx.x; i < 2 * n_r; i += kBlock) s_recs[i] = rsrc[i];
-        if (threadIdx.x == 0) s_recs[2 * n_r] = make_int4(0, 0, 0xff << 16, 0);
-        const double2 *tsrc = reinterpret_cast<const double2 *>(terms) + sb.t_begin;
-        for (int i = threadIdx.x; i < n_t; i += kBlock) s_terms[i] = tsrc[i];
-    }
-    __syncthreads();
-    const double in_scale = norm_src ? 1.0 / *norm_src : 1.0;
-    const double prev_scale = fuse_prev ? (*norm_src) / (*norm_prev) : 0.0;
-    const char *src_lo = reinterpret_cast<const char *>(src + lo);
-    char *dst_lo = reinterpret_cast<char *>(dst + lo);
-    const bool reads_dst = !first || fuse_prev;
-
-    for (unsigned t = blockIdx.x; t < tile_count; t += gridDim.x) {
-        const unsigned rep = tile_rep(sb, t);
-        const unsigned base = rep ^ Tc;
-        {
-            double2 a[16];
-#pragma unroll
-            for (int r = 0; r < 16; ++r) {
-                const unsigned hi = base ^ ((r & 1) ? rb0 : 0u) ^ ((r & 2) ? rb1 : 0u) ^ ((r & 4) ? rb2 : 0u) ^ ((r & 8) ? rb3 : 0u);
-                a[r] = __ldcs(reinterpret_cast<const double2 *>(src_lo + (unsigned long long)hi * chunk_bytes));
-            }
-            __syncthreads();
-#pragma unroll
-            for (int r = 0; r < 16; ++r) tile[((unsigned)r << 8) | v0] = a[r];
-        }
-        __syncthreads();
-        {   // pull this tile's dst lines and the CTA's next src tile into L2 while the records are being walked
-            const unsigned h0 = rep ^ pcA;
-            if (reads_dst) {
-                prefetch_l2(dst_lo + (unsigned long long)h0 * chunk_bytes);
-                prefetch_l2(dst_lo + (unsigned long long)(h0 ^ rb0) * chunk_bytes);
-            }
-            if (t + gridDim.x < tile_count) {
-                const unsigned h1 = tile_rep(sb, t + gridDim.x) ^ pcA;
-                prefetch_l2(src_lo + (unsigned long long)h1 * chunk_bytes);
-                prefetch_l2(src_lo + (unsigned long long)(h1 ^ rb0) * chunk_bytes);
-            }
-        }
-        double2 acc[16];
-#pragma unroll
-        for (int r = 0; r < 16; ++r) acc[r] = make_double2(0.0, 0.0);
-        {
-            int gi = 0;
-            int4 ra = s_recs[0], rb = s_recs[1];
-            apply_runs<0>(acc, tile, v0, rep, s_recs, s_terms, gi, ra, rb);
-        }
-#pragma unroll
-        for (int r = 0; r < 16; ++r) {
-            const unsigned hi = base ^ ((r & 1) ? rb0 : 0u) ^ ((r & 2) ? rb1 : 0u) ^ ((r & 4) ? rb2 : 0u) ^ ((r & 8) ? rb3 : 0u);
-            double2 *p = reinterpret_cast<double2 *>(dst_lo + (unsigned long long)hi * chunk_bytes);
-            double2 o = make_double2(acc[r].x * in_scale, acc[r].y * in_scale);
-            if (first) {
-                if (fuse_prev) {
-                    const double2 q = *p;
-                    o.x -= prev_scale * q.x;
-                    o.y -= prev_scale * q.y;
-                }
-            } else {
-                const double2 q = *p;
-                o.x += q.x;
-                o.y += q.y;
-            }
-            __stcs(p, o);
-        }
-    }
 }
 
 }  // namespace b200vqe

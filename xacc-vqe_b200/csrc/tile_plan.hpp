@@ -661,7 +661,8 @@ inline TilePlanOpts apply_plan_opts(int planner = 2) {
 // Records of the tile kernels for a plan built with the kStage* capacities.  allow_pure (expectation plans built with
 // shear): a record whose sheared flip mask has no thread part gets key + 32 -- the kernel then takes the partner from
 // the thread's own registers.
-inline void build_tile_records(TilePlan &P, bool allow_pure = false, bool fuse = false) {
+// apply_keys (H psi plans, k_tile_apply_pipe8): key = which * 8 + (XR & 7); bit 3 of XR stays a run-time quantity (xv bit 11).
+inline void build_tile_records(TilePlan &P, bool allow_pure = false, bool fuse = false, bool apply_keys = false) {
     P.recs.clear();
     P.fused = fuse;
     constexpr unsigned tmask = (1u << kTileThreadBits) - 1;
@@ -710,7 +711,7 @@ inline void build_tile_records(TilePlan &P, bool allow_pure = false, bool fuse =
                 r.kb = kb - (uint32_t)B.t_begin;
                 r.count = cnt;
                 r.xv = tg.xv;
-                r.key = (uint8_t)((pure ? 32 : 0) + which * 16 + (xr ? xr - 1 : 15));
+                r.key = apply_keys ? (uint8_t)(which * 8 + (xr & 7)) : (uint8_t)((pure ? 32 : 0) + which * 16 + (xr ? xr - 1 : 15));
                 r.view = view;
                 r.packed0 = P.terms[kb].packed;
                 r.u0 = P.terms[kb].u;
