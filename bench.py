@@ -298,7 +298,10 @@ def run_gpu(args):
     be = xb.Backend(n, device=local_rank, rank=rank, world=world, comm_id=comm_id)
     be.set_option("expect-engine", args.engine)
     be.set_option("apply-engine", args.engine)
-    be.set_option("tile-chunk-bits", args.chunk_bits)
+    if args.chunk_bits is not None:
+        be.set_option("tile-chunk-bits", args.chunk_bits)
+    if args.apply_chunk_bits is not None:
+        be.set_option("apply-chunk-bits", args.apply_chunk_bits)
     be.set_option("tile-bits", args.tile_bits)
     be.set_option("tile-ctas-per-sm", args.tile_ctas)
     be.set_option("tile-planner", args.planner)
@@ -616,7 +619,8 @@ def main():
     ap.add_argument("--expect-kernel", default="auto", choices=["auto", "pipe", "classic"])
     ap.add_argument("--dispatch", type=int, default=1, choices=[0, 1, 2, 3])
     ap.add_argument("--planner", type=int, default=3, choices=[1, 2, 3], help="tile planner version (csrc/tile_plan.hpp)")
-    ap.add_argument("--chunk-bits", type=int, default=3, help="tile engine: log2 contiguous amplitudes per HBM chunk")
+    ap.add_argument("--chunk-bits", type=int, default=None, help="tile engine: log2 contiguous amplitudes per HBM chunk (library default: 3 for <psi|H|psi>, 4 for H psi)")
+    ap.add_argument("--apply-chunk-bits", type=int, default=None, help="the same for the H psi plans only")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

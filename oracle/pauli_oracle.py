@@ -833,55 +833,79 @@ def rdm_energy(rho: np.ndarray, e_nuc: float, hpq: np.ndarray, hpqrs: np.ndarray
 #  criteria task/tasks/VQEMinimizeTask.hpp:74-104)
 # --------------------------------------------------------------------------
 def nelder_mead(fun, x0: Sequence[float], f_delta: float = 1e-6, iterations: int = 10000):
+    """tpls/cppnumericalsolvers/cppoptlib/solver/neldermeadsolver.h:47-194, literally:
+      * initial simplex (:23-41); loop bound iterations * DIM (:71) but the solver's OWN checkConvergence (:208-219, no gradient
+        test) ends the walk once iter > iterations (:209) or max_i |f_i - f_best| < fDelta (:215);
+      * second stop (:109-115): spread of f <= tt1 AND spread of x <= tt2, both thresholds max(1e-4, 10 ulp-ish) (:88-90);
+      * reflect / expand / outside contraction (f_c <= f_r) / inside contraction (f_c < f_worst, STRICT) / shrink (:130-177);
+      * shrink re-evaluates the best vertex as well (:199);
+    criteria from task/tasks/VQEMinimizeTask.hpp:74-104 (fDelta 1e-6, iterations 10000, xDelta 0).
+    Returns (best vertex, LAST evaluated objective value, iterations): CppOptVQEBackend::minimize reports currentEnergy, the
+    value of the most recent call of value() (VQEMinimizeTask.hpp:44,50-53), not f at the best vertex."""
     x0 = np.asarray(x0, dtype=np.float64)
     dim = x0.shape[0]
     rho, xi, gam = 1.0, 2.0, 0.5
+    last = [None]
+
+    def ev(x):
+        last[0] = float(fun(np.array(x, dtype=np.float64)))
+        return last[0]
+
     S = np.tile(x0[:, None], (1, dim + 1))
     for c in range(1, dim + 1):
         r = c - 1
         S[r, c] = 0.00025 if x0[r] == 0 else 1.05 * x0[r]
-    f = [fun(S[:, i].copy()) for i in range(dim + 1)]
+    f = [ev(S[:, i]) for i in range(dim + 1)]
     index = sorted(range(dim + 1), key=lambda a: f[a])
+    eps = np.finfo(np.float64).eps
     it = 0
     max_iter = iterations * dim
     while it < max_iter:
-        max1 = max(abs(f[index[i]] - f[index[0]]) for i in range(1, dim + 1))
-        if it > 0 and max1 < f_delta:
-            break
         best, worst = index[0], index[dim]
+        max1 = max(abs(f[index[i]] - f[best]) for i in range(1, dim + 1))
+        max2 = max(float(np.max(np.abs(S[:, index[i]] - S[:, best]))) for i in range(1, dim + 1))
+        xb = float(np.max(S[:, best]))
+        tt1 = max(1e-4, 10 * np.nextafter(f[best], eps) - f[best])
+        tt2 = max(1e-4, 10 * (np.nextafter(xb, eps) - xb))
+        if iterations != 0 and (it > iterations or (f_delta > 0 and max1 < f_delta)):
+            break
+        if max1 <= tt1 and max2 <= tt2:
+            break
         x_bar = np.sum(S[:, index[:dim]], axis=1) / dim
         x_r = (1 + rho) * x_bar - rho * S[:, worst]
-        f_r = fun(x_r)
+        f_r = ev(x_r)
+        shrink = False
         if f_r < f[best]:
             x_e = (1 + rho * xi) * x_bar - rho * xi * S[:, worst]
-            f_e = fun(x_e)
+            f_e = ev(x_e)
             if f_e < f_r:
                 S[:, worst], f[worst] = x_e, f_e
             else:
                 S[:, worst], f[worst] = x_r, f_r
         elif f_r < f[index[dim - 1]]:
             S[:, worst], f[worst] = x_r, f_r
-        else:
-            done = False
-            if f_r < f[worst]:
-                x_c = (1 + rho * gam) * x_bar - rho * gam * S[:, worst]
-                f_c = fun(x_c)
-                if f_c <= f_r:
-                    S[:, worst], f[worst] = x_c, f_c
-                    done = True
+        elif f_r < f[worst]:
+            x_c = (1 + rho * gam) * x_bar - rho * gam * S[:, worst]
+            f_c = ev(x_c)
+            if f_c <= f_r:
+                S[:, worst], f[worst] = x_c, f_c
             else:
-                x_c = (1 - gam) * x_bar + gam * S[:, worst]
-                f_c = fun(x_c)
-                if f_c <= f[worst]:
-                    S[:, worst], f[worst] = x_c, f_c
-                    done = True
-            if not done:
-                for i in range(1, dim + 1):
-                    S[:, index[i]] = S[:, best] + 0.5 * (S[:, index[i]] - S[:, best])
-                    f[index[i]] = fun(S[:, index[i]].copy())
+                shrink = True
+        else:
+            x_c = (1 - gam) * x_bar + gam * S[:, worst]
+            f_c = ev(x_c)
+            if f_c < f[worst]:
+                S[:, worst], f[worst] = x_c, f_c
+            else:
+                shrink = True
+        if shrink:
+            f[best] = ev(S[:, best])
+            for i in range(1, dim + 1):
+                S[:, index[i]] = 0.5 * S[:, index[i]] + 0.5 * S[:, best]
+                f[index[i]] = ev(S[:, index[i]])
         index = sorted(range(dim + 1), key=lambda a: f[a])
         it += 1
-    return S[:, index[0]].copy(), f[index[0]], it
+    return S[:, index[0]].copy(), last[0], it
 
 
 # --------------------------------------------------------------------------

@@ -338,6 +338,73 @@ def test_lanczos_vs_dense(xb, n, T, seed):
     assert np.linalg.norm(hv - e0 * vec) < 1e-7 * np.abs(cf).sum()
 
 
+def test_config3_molecule_shaped_14_qubit_lanczos(xb):
+    """BASELINE configs[2] at its stated shape: 14-qubit JW molecule-shaped Hamiltonian (7 spatial orbitals, seed 14; the
+    reference ships no H2O integrals), Lanczos ground state with tol 1e-12 on the Ritz residual in the full space and in the
+    6-electron sector (diag-number-symmetry, task/tasks/DiagonalizeTask.cpp:54-183), against ARPACK over the C oracle.
+    |E0| is O(10), so these are true RELATIVE errors (north star: 1e-10)."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    from bench_sweep import lih_shaped_source
+    from scipy.sparse.linalg import LinearOperator, eigsh
+    n, ne = 14, 6
+    op = xb.compile(lih_shaped_source(n, seed=14), "jw", n)
+    xm, zm, cf = op.pack()
+    be = xb.Backend(n)
+    be.set_hamiltonian(xm, zm, cf)
+    T, G = be.hamiltonian_stats()
+    assert T > 1000 and G < T // 4                       # molecule-shaped: many terms per xmask group
+    want, _ = po.ground_state_eigsh(xm, zm, cf, n, tol=1e-13, apply=lambda v: co.apply(n, xm, zm, cf, v))
+    e0, it, res = be.lanczos_ground(tol=1e-12, max_iter=2000, seed=14)
+    assert abs(want) > 1.0 and abs(e0 - want) / abs(want) < REL and res < 1e-10 * abs(e0)
+    idx = np.array([j for j in range(1 << n) if bin(j).count("1") == ne])
+
+    def mv(v):
+        full = np.zeros(1 << n, complex)
+        full[idx] = v
+        return co.apply(n, xm, zm, cf, full)[idx]
+    ws = eigsh(LinearOperator((len(idx), len(idx)), matvec=mv, dtype=complex), k=1, which="SA", tol=1e-13)[0][0]
+    be.set_number_sector(ne, "jw")
+    es, its, _ = be.lanczos_ground(tol=1e-12, max_iter=2000, seed=14)
+    assert abs(es - ws) / abs(ws) < REL and es >= e0 - 1e-9
+    # the energy of the sector ground state through <psi|H|psi>, both engines, relative to |E|
+    be.set_number_sector(-1)
+    be.set_number_sector(ne, "jw")
+    es2, _, _ = be.lanczos_ground(tol=1e-12, max_iter=2000, seed=14, want_vector=True)
+    be.set_number_sector(-1)
+    e_tile = be.expectation().real
+    be.set_option("expect-engine", "stream")
+    be.set_hamiltonian(xm, zm, cf)
+    e_stream = be.expectation().real
+    assert abs(e_tile - es2) / abs(es2) < 1e-9 and abs(e_stream - e_tile) / abs(e_tile) < REL
+    be.close()
+
+
+def test_large_register_random_state_vs_oracle(xb):
+    """a normalised complex Gaussian state on a large register -- 26 qubits, 1 GB, 64 random terms --
+    <psi|H|psi>, every <P_k> and H psi against the C oracle (seconds on the host cores).  28 qubits are checked on a product
+    state (test_full_size_register_few_terms_product_state) and, in bench.py, on a random state against a 256-term sample."""
+    n, T, seed = 26, 64, 2628
+    xm, zm, cf = random_hamiltonian(n, T, seed)
+    be = xb.Backend(n)
+    be.n_slots(2)
+    be.set_hamiltonian(xm, zm, cf)
+    be.random_state(0, seed)
+    psi = be.download(0)
+    assert abs(np.vdot(psi, psi) - 1.0) < 1e-12
+    eo, pero = co.expect(n, xm, zm, cf, psi)
+    e, per = be.expectation(per_term=True)
+    scale = np.abs(cf).sum()
+    assert abs(e - eo) < REL * scale and np.abs(per - pero.real).max() < 1e-11
+    assert abs(be.expectation() - eo) < REL * scale                    # the energy-only path (pipelined kernel, views)
+    be.apply_h(0, 1, want_alpha=False)
+    got = be.download(1)
+    ref = co.apply(n, xm, zm, cf, psi)
+    assert np.abs(got - ref).max() < 1e-12 * scale
+    be.close()
+
+
 def test_text_fixture_ground_states(xb, golden):
     d = golden["derived"]
     for key, want in (("six_qubit_118", d["six_qubit_E0"]), ("four_qubit_100", d["four_qubit_E0"]),
@@ -497,3 +564,55 @@ def test_lanczos_checkpoint_and_resume(xb, tmp_path):
         be3.lanczos_load(path)                                          # wrong register size
     be3.close()
     be2.close()
+
+
+def test_lanczos_checkpoint_is_bound_to_its_problem(xb, tmp_path):
+    """A checkpoint carries a fingerprint of its Hamiltonian and its particle-number sector and is refused by a handle that
+    holds another problem; a public write into one of the two live vectors, a new sector or new slots drop the unfinished
+    run instead of silently continuing it; a corrupt step count is a parse error, not a crash."""
+    n, T, seed = 12, 40, 77
+    xm, zm, cf = random_hamiltonian(n, T, seed)
+    be = xb.Backend(n)
+    be.set_hamiltonian(xm, zm, cf)
+    with pytest.raises(xb.B200Error):
+        be.lanczos_ground(tol=1e-13, max_iter=8, seed=seed)
+    path = str(tmp_path / "a.ckpt")
+    be.lanczos_save(path)
+    # another operator (one coefficient changed)
+    cf2 = cf.copy()
+    cf2[3] *= 1.0000001
+    other = xb.Backend(n)
+    other.set_hamiltonian(xm, zm, cf2)
+    with pytest.raises(xb.B200Error, match="another Hamiltonian"):
+        other.lanczos_load(path)
+    other.set_hamiltonian(xm, zm, cf)
+    other.set_number_sector(3, "jw")
+    with pytest.raises(xb.B200Error, match="sector"):
+        other.lanczos_load(path)                                        # the run was on H, not on P H P
+    other.set_number_sector(-1)
+    other.lanczos_load(path)                                            # the right problem: accepted
+    other.set_number_sector(3, "jw")                                    # ... and dropped again by a new sector
+    with pytest.raises(xb.B200Error, match="nothing to resume"):
+        other.lanczos_ground(tol=1e-11, max_iter=100, resume=True)
+    other.close()
+    # writes into the live vectors (slots 1, 2) and a slot re-allocation invalidate the in-handle run
+    for spoil in (lambda b: b.reset(1, 0), lambda b: b.apply_h(0, 2, want_alpha=False), lambda b: b.n_slots(3)):
+        with pytest.raises(xb.B200Error):
+            be.lanczos_ground(tol=1e-13, max_iter=8, seed=seed)
+        spoil(be)
+        with pytest.raises(xb.B200Error, match="nothing to resume"):
+            be.lanczos_ground(tol=1e-11, max_iter=100, resume=True)
+    be.close()
+    # corrupt step count / truncated file
+    raw = bytearray(open(path, "rb").read())
+    raw[20:24] = (2 ** 30).to_bytes(4, "little")                        # LzHeader.m
+    bad = str(tmp_path / "bad.ckpt")
+    open(bad, "wb").write(bytes(raw))
+    be4 = xb.Backend(n)
+    be4.set_hamiltonian(xm, zm, cf)
+    with pytest.raises(xb.B200Error, match="truncated|corrupt"):
+        be4.lanczos_load(bad)
+    open(bad, "wb").write(open(path, "rb").read()[:4096])
+    with pytest.raises(xb.B200Error):
+        be4.lanczos_load(bad)
+    be4.close()

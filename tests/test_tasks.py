@@ -20,6 +20,27 @@ def test_nelder_mead_walks_the_same_simplex_as_the_oracle():
         assert it == ito and f == fo and np.array_equal(x, xo)
 
 
+def test_nelder_mead_follows_the_reference_solver():
+    """neldermeadsolver.h details that change iteration counts and nQpuCalls: the spread test (f and x spreads <= 1e-4) ends a
+    walk that fDelta = 1e-9 alone would continue; the cap is `iterations` (checkConvergence), not iterations * DIM; the
+    reported energy is the LAST evaluated value; every objective call is counted identically by the mirror and the oracle."""
+    def quad(v):
+        return float((v[0] - 1.0) ** 2 + 3.0 * (v[1] + 0.5) ** 2) - 2.0
+    for fn, arg in ((xb.nelder_mead, None), (po.nelder_mead, None)):
+        calls = []
+        x, f, it = fn(lambda v: (calls.append(np.array(v)), quad(v))[1], [0.0, 0.0], 1e-9, 10000)
+        assert f == quad(calls[-1]) and np.abs(x - [1.0, -0.5]).max() < 2e-3
+        # stopped by the 1e-4 spread rule: a tighter simplex than 1e-4 would need many more steps
+        assert 10 < it < 80, it
+        xc, fc, itc = fn(quad, [0.0, 0.0], 1e-12, 5)
+        assert itc == 6                      # iter > iterations is tested before the step: steps 0..5 run
+    a = []
+    b = []
+    xb.nelder_mead(lambda v: (a.append(tuple(v)), quad(v))[1], [0.3, -0.2], 1e-9, 300)
+    po.nelder_mead(lambda v: (b.append(tuple(v)), quad(v))[1], [0.3, -0.2], 1e-9, 300)
+    assert a == b and len(a) > 20
+
+
 def test_parameter_generation_and_result_persist(tmp_path):
     from xaccvqe_b200.tasks import generate_parameters
     assert generate_parameters(2, "0.0,-0.0571583356234").tolist() == [0.0, -0.0571583356234]
@@ -63,6 +84,8 @@ def test_execute_rejects_bad_arguments(golden):
         xb.execute(op, None, task="no-such-task")
     with pytest.raises(xb.B200Error):
         xb.execute(op, None, task="compute-energy", ansatz="uccsd")      # n-electrons missing (UCCSD.cpp:16-22)
+    with pytest.raises(xb.B200Error, match="disagree"):                   # one option drives compiler, UCCSD and sector rows
+        xb.execute(golden["h2_source"], None, **{"transformation": "jw", "fermion-transformation": "bk"})
 
 
 # ------------------------------------------------------------------ GPU: the reference's scenarios
@@ -75,6 +98,17 @@ def test_diagonalize_task_h2_exact(golden):
     assert abs(buf.getInformation("vqe-energy") - r.energy) == 0.0
     r2 = xb.execute(golden["h2_source"], None, **{"task": "vqe-diagonalize", "n-qubits": 4})
     assert abs(r2.energy - r.energy) < 1e-12
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tr", ["jw", "bk"])
+def test_both_spellings_of_the_transformation_option_agree(golden, tr):
+    """'transformation' (python kwarg) and 'fermion-transformation' (the option it sets, python/xacc-vqe-py.cpp:406-408) select
+    the same operator AND the same number-symmetry rows when the source is compiled inside execute()."""
+    kw = {"task": "vqe-diagonalize", "diag-number-symmetry": True, "n-electrons": 2}
+    a = xb.execute(golden["h2_source"], None, **dict(kw, **{"transformation": tr}))
+    b = xb.execute(golden["h2_source"], None, **dict(kw, **{"fermion-transformation": tr}))
+    assert a.energy == b.energy and abs(a.energy - golden["h2_ground_energy_exact"]) < 1e-10
 
 
 @pytest.mark.gpu

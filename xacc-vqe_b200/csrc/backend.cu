@@ -12,6 +12,8 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <new>
+#include <stdexcept>
 #include <dlfcn.h>
 #include <numeric>
 
@@ -79,7 +81,28 @@ thread_local std::string g_err;
         }                                                                                          \
     } while (0)
 #define FAIL(code, msg) do { h->err = (msg); return (code); } while (0)
+
+// Every extern "C" body runs inside this guard: no C++ exception crosses the C ABI (std::bad_alloc of a host vector sized from
+// caller- or file-supplied counts becomes B200VQE_ENOMEM, anything else B200VQE_EINVAL with the message kept for last_error).
+template <class F>
+static int guarded(b200vqe_ctx *h, F &&body) noexcept {
+    try {
+        return body();
+    } catch (const std::bad_alloc &) {
+        (h ? h->err : g_err) = "out of host memory";
+        return B200VQE_ENOMEM;
+    } catch (const std::exception &e) {
+        (h ? h->err : g_err) = std::string("internal error: ") + e.what();
+        return B200VQE_EINVAL;
+    } catch (...) {
+        (h ? h->err : g_err) = "internal error";
+        return B200VQE_EINVAL;
+    }
+}
 #define LAUNCHED(h) do { ++(h)->launches; CK(cudaGetLastError()); } while (0)
+
+// A public call that writes slot 1 or 2 destroys the two live vectors of an unfinished Lanczos run kept for resume / checkpoint.
+static inline void writes_slot(b200vqe_ctx *h, int slot) { if (slot == 1 || slot == 2) h->lz_m = -1; }
 
 static int grid_for(const b200vqe_ctx *h, uint64_t work_items, int per_sm) {
     const uint64_t cap = (uint64_t)h->n_sm * per_sm;
@@ -197,6 +220,7 @@ extern "C" {
 const char *b200vqe_global_error(void) { return g_err.c_str(); }
 
 int b200vqe_comm_unique_id(char id[128]) {
+    return guarded(nullptr, [&]() -> int {
     if (!g_nccl.load(g_err)) return B200VQE_ECOMM;
     ncclUniqueId u;
     static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
@@ -204,6 +228,7 @@ int b200vqe_comm_unique_id(char id[128]) {
     if (r != ncclSuccess) { g_err = g_nccl.GetErrorString(r); return B200VQE_ECOMM; }
     memcpy(id, &u, 128);
     return 0;
+    });
 }
 
 static int create_common(int n_qubits, int device, int rank, int world, const char *id, b200vqe_handle *out) {
@@ -278,14 +303,19 @@ static int create_common(int n_qubits, int device, int rank, int world, const ch
 }
 
 int b200vqe_create(int n_qubits, int device, b200vqe_handle *out) {
+    return guarded(nullptr, [&]() -> int {
     return create_common(n_qubits, device, 0, 1, nullptr, out);
+    });
 }
 int b200vqe_create_sharded(int n_qubits, int device, int rank, int world, const char id[128], b200vqe_handle *out) {
+    return guarded(nullptr, [&]() -> int {
     if (world > 1 && !id) { g_err = "id is NULL"; return B200VQE_EINVAL; }
     return create_common(n_qubits, device, rank, world, id, out);
+    });
 }
 
 int b200vqe_destroy(b200vqe_handle h) {
+    return guarded(h, [&]() -> int {
     if (!h) return 0;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
@@ -307,28 +337,35 @@ int b200vqe_destroy(b200vqe_handle h) {
     cudaStreamDestroy(h->stream);
     delete h;
     return 0;
+    });
 }
 
 const char *b200vqe_last_error(b200vqe_handle h) { return h ? h->err.c_str() : g_err.c_str(); }
 
 int b200vqe_n_slots(b200vqe_handle h, int n_slots) {
+    return guarded(h, [&]() -> int {
     if (!h) return B200VQE_EINVAL;
+    h->lz_m = -1;               // slots may be released below: an unfinished Lanczos run does not survive
     if (n_slots < 1 || n_slots > 16) FAIL(B200VQE_EINVAL, "n_slots must be in [1, 16]");
     CK(cudaSetDevice(h->device));
     for (int s = n_slots; s < (int)h->slots.size(); ++s) if (h->slots[s]) { cudaFree(h->slots[s]); }
     h->slots.resize(n_slots, nullptr);
     return 0;
+    });
 }
 
 int b200vqe_local_amplitudes(b200vqe_handle h, uint64_t *count, uint64_t *first_index) {
+    return guarded(h, [&]() -> int {
     if (!h) return B200VQE_EINVAL;
     if (count) *count = h->nloc;
     if (first_index) *first_index = (uint64_t)h->rank << h->nl;
     return 0;
+    });
 }
 
 // string options in the manner of xacc::setOption(key, value)
 int b200vqe_set_option(b200vqe_handle h, const char *key, const char *value) {
+    return guarded(h, [&]() -> int {
     if (!h) return B200VQE_EINVAL;
     if (!key || !value) FAIL(B200VQE_EINVAL, "null option key / value");
     const std::string k(key), v(value);
@@ -350,6 +387,13 @@ int b200vqe_set_option(b200vqe_handle h, const char *key, const char *value) {
         const int c = atoi(value);
         if (c < 2 || c > 8) FAIL(B200VQE_EINVAL, "tile-chunk-bits must be in [2, 8]");
         h->opt_tile_chunk_bits = c;
+        h->opt_apply_chunk_bits = c;        // an explicit choice applies to both engines
+        return 0;
+    }
+    if (k == "apply-chunk-bits") {
+        const int c = atoi(value);
+        if (c < 2 || c > 8) FAIL(B200VQE_EINVAL, "apply-chunk-bits must be in [2, 8]");
+        h->opt_apply_chunk_bits = c;
         return 0;
     }
     if (k == "shard-exchange") {
@@ -390,32 +434,42 @@ int b200vqe_set_option(b200vqe_handle h, const char *key, const char *value) {
         return 0;
     }
     FAIL(B200VQE_EINVAL, "unknown option '" + k + "'");
+    });
 }
 
 int b200vqe_synchronize(b200vqe_handle h) {
+    return guarded(h, [&]() -> int {
     if (!h) return B200VQE_EINVAL;
     CK(cudaSetDevice(h->device));
     CK(cudaStreamSynchronize(h->stream));
     return 0;
+    });
 }
 int b200vqe_kernel_launches(b200vqe_handle h, int64_t *count) {
+    return guarded(h, [&]() -> int {
     if (!h || !count) return B200VQE_EINVAL;
     *count = h->launches;
     return 0;
+    });
 }
 int b200vqe_last_kernel_ms(b200vqe_handle h, double *ms) {
+    return guarded(h, [&]() -> int {
     if (!h || !ms) return B200VQE_EINVAL;
     *ms = h->last_ms;
     return 0;
+    });
 }
 
 int b200vqe_timer_start(b200vqe_handle h) {
+    return guarded(h, [&]() -> int {
     if (!h) return B200VQE_EINVAL;
     CK(cudaSetDevice(h->device));
     CK(cudaEventRecord(h->ev_t0, h->stream));
     return 0;
+    });
 }
 int b200vqe_timer_stop(b200vqe_handle h, double *ms) {
+    return guarded(h, [&]() -> int {
     if (!h || !ms) return B200VQE_EINVAL;
     CK(cudaSetDevice(h->device));
     CK(cudaEventRecord(h->ev_t1, h->stream));
@@ -424,6 +478,7 @@ int b200vqe_timer_stop(b200vqe_handle h, double *ms) {
     CK(cudaEventElapsedTime(&f, h->ev_t0, h->ev_t1));
     *ms = f;
     return 0;
+    });
 }
 
 }  // extern "C"

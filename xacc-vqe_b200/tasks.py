@@ -258,67 +258,75 @@ class DiagonalizeTask:
         return VQETaskResult(energy=e0, angles=np.asarray(parameters, float), vqeIterations=it)
 
 
-def nelder_mead(fun: Callable[[np.ndarray], float], x0: Sequence[float], f_delta: float = 1e-6, iterations: int = 10000,
-                reference_gradnorm_quirk: bool = False):
-    """The simplex the reference's optimiser walks (tpls/cppnumericalsolvers/cppoptlib/solver/neldermeadsolver.h:23-190), with
-    its arithmetic: vertex c = x0 with coordinate c-1 scaled by 1.05 (0.00025 when zero); x_bar = mean of the best DIM
-    vertices; reflect (1+rho) x_bar - rho x_w, expand (1+rho xi), contract (1 +- rho gam), shrink 0.5; rho=1, xi=2, gam=0.5;
-    stop when max_i |f_i - f_best| < fDelta or after iterations*DIM steps (criteria of task/tasks/VQEMinimizeTask.hpp:74-104).
-
-    reference_gradnorm_quirk=True reproduces the literal stop rule: VQECriteria sets gradNorm = 1e-4 while the simplex solver
-    never updates its current gradNorm (0 after reset, cppoptlib/meta.h:96-125), so checkConvergence reports
-    GradNormTolerance at the first check and the reference returns the best vertex of the INITIAL simplex.  Default False:
-    the simplex is actually walked."""
+def nelder_mead(fun: Callable[[np.ndarray], float], x0: Sequence[float], f_delta: float = 1e-6, iterations: int = 10000):
+    """The simplex walk of the reference's optimiser (tpls/cppnumericalsolvers/cppoptlib/solver/neldermeadsolver.h:47-194) with
+    its arithmetic and its stop rules, so that iteration counts and nQpuCalls match:
+      vertex c = x0 with coordinate c-1 scaled by 1.05 (0.00025 when zero); x_bar = mean of the best DIM vertices;
+      reflect (1+rho) x_bar - rho x_w, expand (1+rho xi), contract outside (accepted when f_c <= f_r) / inside (accepted only
+      when f_c < f_worst), else shrink by 0.5 towards the best vertex, which is re-evaluated too (:196-204); rho=1, xi=2, gam=0.5.
+      Stop (checked before every step): iter > iterations, or spread of f below fDelta (the solver's own checkConvergence,
+      :208-219: it has no gradient test, so VQECriteria's gradNorm = 1e-4 is never consulted), or spread of f <= tt1 and
+      spread of x <= tt2 (:88-115; tt1 = max(1e-4, 10 * nextafter(f_best, eps) - f_best) exactly as written there,
+      tt2 = max(1e-4, 10 ulp of the largest coordinate)); criteria defaults from task/tasks/VQEMinimizeTask.hpp:74-104.
+    Returns (best vertex, last evaluated objective value, iterations): CppOptVQEBackend::minimize reports currentEnergy, the
+    value of its most recent value() call (VQEMinimizeTask.hpp:44), not f at the best vertex."""
     rho, xi, gam = 1.0, 2.0, 0.5
     x0 = np.asarray(x0, float)
     d = len(x0)
+    calls = {"last": 0.0}
+
+    def value(x):
+        calls["last"] = float(fun(np.array(x, float)))
+        return calls["last"]
+
     if d == 0:
-        return x0, float(fun(x0)), 0
+        return x0, value(x0), 0
     S = np.repeat(x0[:, None], d + 1, axis=1)              # columns are vertices, as in the reference
     for c in range(1, d + 1):
         S[c - 1, c] = 0.00025 if x0[c - 1] == 0 else (1 + 0.05) * x0[c - 1]
-    f = [float(fun(S[:, i].copy())) for i in range(d + 1)]
-    index = sorted(range(d + 1), key=lambda a: f[a])
+    f = [value(S[:, i]) for i in range(d + 1)]
+    order = sorted(range(d + 1), key=lambda a: f[a])
+    eps = float(np.finfo(float).eps)
     it = 0
     while it < iterations * d:
-        max1 = max(abs(f[index[i]] - f[index[0]]) for i in range(1, d + 1))
-        if reference_gradnorm_quirk or (it > 0 and max1 < f_delta):
+        lo, hi = order[0], order[d]
+        spread_f = max(abs(f[k] - f[lo]) for k in order[1:])
+        spread_x = max(float(np.abs(S[:, k] - S[:, lo]).max()) for k in order[1:])
+        if iterations != 0 and (it > iterations or (f_delta > 0 and spread_f < f_delta)):
             break
-        best, worst = index[0], index[d]
-        x_bar = np.zeros(d)
-        for i in range(d):
-            x_bar = x_bar + S[:, index[i]]
-        x_bar = x_bar / d
-        x_r = (1 + rho) * x_bar - rho * S[:, worst]
-        f_r = float(fun(x_r))
-        if f_r < f[best]:
-            x_e = (1 + rho * xi) * x_bar - rho * xi * S[:, worst]
-            f_e = float(fun(x_e))
-            if f_e < f_r:
-                S[:, worst], f[worst] = x_e, f_e
-            else:
-                S[:, worst], f[worst] = x_r, f_r
-        elif f_r < f[index[d - 1]]:
-            S[:, worst], f[worst] = x_r, f_r
+        top = float(S[:, lo].max())
+        if spread_f <= max(1e-4, 10 * float(np.nextafter(f[lo], eps)) - f[lo]) and spread_x <= max(1e-4, 10 * (float(np.nextafter(top, eps)) - top)):
+            break
+        x_bar = sum(S[:, k] for k in order[:d]) / d
+        x_r = (1 + rho) * x_bar - rho * S[:, hi]
+        f_r = value(x_r)
+        accepted = None
+        if f_r < f[lo]:
+            x_e = (1 + rho * xi) * x_bar - rho * xi * S[:, hi]
+            f_e = value(x_e)
+            accepted = (x_e, f_e) if f_e < f_r else (x_r, f_r)
+        elif f_r < f[order[d - 1]]:
+            accepted = (x_r, f_r)
+        elif f_r < f[hi]:
+            x_c = (1 + rho * gam) * x_bar - rho * gam * S[:, hi]          # outside contraction
+            f_c = value(x_c)
+            if f_c <= f_r:
+                accepted = (x_c, f_c)
         else:
-            placed = False
-            if f_r < f[worst]:
-                x_c = (1 + rho * gam) * x_bar - rho * gam * S[:, worst]          # outside contraction
-                f_c = float(fun(x_c))
-                if f_c <= f_r:
-                    S[:, worst], f[worst], placed = x_c, f_c, True
-            else:
-                x_c = (1 - gam) * x_bar + gam * S[:, worst]                     # inside contraction
-                f_c = float(fun(x_c))
-                if f_c <= f[worst]:
-                    S[:, worst], f[worst], placed = x_c, f_c, True
-            if not placed:
-                for i in range(1, d + 1):
-                    S[:, index[i]] = S[:, best] + 0.5 * (S[:, index[i]] - S[:, best])
-                    f[index[i]] = float(fun(S[:, index[i]].copy()))
-        index = sorted(range(d + 1), key=lambda a: f[a])
+            x_c = (1 - gam) * x_bar + gam * S[:, hi]                     # inside contraction
+            f_c = value(x_c)
+            if f_c < f[hi]:
+                accepted = (x_c, f_c)
+        if accepted is not None:
+            S[:, hi], f[hi] = accepted
+        else:                                                            # shrink towards the best vertex
+            f[lo] = value(S[:, lo])
+            for k in order[1:]:
+                S[:, k] = 0.5 * S[:, k] + 0.5 * S[:, lo]
+                f[k] = value(S[:, k])
+        order = sorted(range(d + 1), key=lambda a: f[a])
         it += 1
-    return S[:, index[0]].copy(), f[index[0]], it
+    return S[:, order[0]].copy(), calls["last"], it
 
 
 class VQEMinimizeTask:
@@ -345,8 +353,13 @@ def execute(op, buffer: Optional[AcceleratorBuffer] = None, **kwargs) -> VQETask
     vqe-iterations, vqe-persist-data, device.  'accelerator' and 'mpi-provider' are accepted and ignored: the accelerator is
     the B200 statevector backend, the communicator is NCCL inside a sharded handle."""
     kw = {k.replace("_", "-"): v for k, v in kwargs.items()}
+    # ONE fermion transformation drives the compiler, the UCCSD generator and the number-symmetry rows, as the reference's single
+    # option 'fermion-transformation' does (set from the kwarg 'transformation', python/xacc-vqe-py.cpp:406-408)
+    tr = str(kw.get("transformation", kw.get("fermion-transformation", "jw")))
+    if "transformation" in kw and "fermion-transformation" in kw and str(kw["transformation"]) != str(kw["fermion-transformation"]):
+        raise B200Error(-1, "'transformation' and 'fermion-transformation' disagree")
     if isinstance(op, str):
-        op = compile(op, kw.get("transformation", "jw"))
+        op = compile(op, tr)
     task = kw.get("task", "vqe-diagonalize")           # default task (:178)
     if task not in TASKS:
         raise B200Error(-1, f"unknown task '{task}' (have {sorted(TASKS)})")
@@ -360,7 +373,7 @@ def execute(op, buffer: Optional[AcceleratorBuffer] = None, **kwargs) -> VQETask
             raise B200Error(-1, f"unknown ansatz '{ansatz}'")
         if "n-electrons" not in kw:
             raise B200Error(-1, "the uccsd ansatz needs 'n-electrons'")     # UCCSD.cpp:16-22
-        ansatz = Ansatz.uccsd(n_qubits, int(kw["n-electrons"]), kw.get("transformation", "jw"))
+        ansatz = Ansatz.uccsd(n_qubits, int(kw["n-electrons"]), tr)
     program = VQEProgram(op, n_qubits, ansatz, device=int(kw.get("device", 0)))
     if buffer is not None:
         buffer.n_qubits = n_qubits
@@ -369,7 +382,7 @@ def execute(op, buffer: Optional[AcceleratorBuffer] = None, **kwargs) -> VQETask
         sym = bool(kw.get("diag-number-symmetry", False)) and "n-electrons" in kw        # both options, as DiagonalizeTask.cpp:54-55
         t = DiagonalizeTask(program, buffer, want_vector=bool(kw.get("print-ground-state", False)),
                             n_electrons=int(kw["n-electrons"]) if sym else None,
-                            transformation=str(kw.get("fermion-transformation", kw.get("transformation", "jw"))))
+                            transformation=tr)
     elif task == "compute-energy":
         t = ComputeEnergyVQETask(program, buffer, persist_file=str(kw.get("vqe-persist-data", "")))
     else:
