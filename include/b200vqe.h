@@ -122,10 +122,12 @@ int b200vqe_hamiltonian_stats(b200vqe_handle h, int64_t *n_terms, int64_t *n_gro
  * out[1] xmask groups, out[2] batches of H psi (0 until the first H psi plans them), out[3] x_rank classes of a sharded
  * <psi|H|psi>, out[4] chunk bits, out[5] tile bits. */
 int b200vqe_plan_stats(b200vqe_handle h, int64_t out[6]);
-/* NVLink exchange of the last sharded b200vqe_expectation: CUDA-event time [ms] of the slab swaps on the communication stream
- * (summed) and the bytes this rank received.  The counterpart of the reference's only collective is the final all-reduce
+/* NVLink exchange of the last sharded b200vqe_expectation / b200vqe_apply_h / Lanczos step: CUDA-event time [ms] of the transfers on
+ * the communication stream (summed) and the bytes this rank received.  The counterpart of the reference's only collective is the final all-reduce
  * (task/tasks/ComputeEnergyVQETask.cpp:114-126). */
 int b200vqe_last_exchange(b200vqe_handle h, double *ms, double *bytes);
+/* ... and the time [ms] the compute stream WAITED for those transfers (what the kernels queued before each wait did not hide). */
+int b200vqe_last_exchange_exposed(b200vqe_handle h, double *ms);
 
 /* Host-only view of the tile-engine plan (see csrc/tile_plan.hpp) for a Hermitian term list, exactly as
  * b200vqe_set_hamiltonian builds it for <psi|H|psi> (batch capacities included): raw TileBatch[160 B],

@@ -262,10 +262,16 @@ class Backend:
         return dict(zip(("expect_batches", "groups", "apply_batches", "expect_classes", "chunk_bits", "tile_bits"), [int(v) for v in out]))
 
     def last_exchange(self):
-        """(ms, bytes received by this rank) of the NVLink slab swaps of the last sharded <psi|H|psi>."""
+        """(ms, bytes received by this rank) of the NVLink transfers of the last sharded <psi|H|psi> / H psi."""
         ms, by = C.c_double(), C.c_double()
         self._ck(lib().b200vqe_last_exchange(self.h, C.byref(ms), C.byref(by)))
         return ms.value, by.value
+
+    def last_exchange_exposed(self) -> float:
+        """ms the compute stream waited for the NVLink transfers of the last sharded <psi|H|psi> / H psi (the un-hidden part)."""
+        ms = C.c_double()
+        self._ck(lib().b200vqe_last_exchange_exposed(self.h, C.byref(ms)))
+        return ms.value
 
     def reset(self, slot: int = 0, basis_index: int = 0):
         self._ck(lib().b200vqe_state_reset(self.h, C.c_int(slot), C.c_uint64(basis_index)))

@@ -140,7 +140,10 @@ static int make_slabs(b200vqe_ctx *h, const double2 *src, Slabs &s) {
     // without waiting; wait_gather() orders the main stream after it before the first remote read
     CK(cudaEventRecord(h->ev_src_ready, h->stream));
     CK(cudaStreamWaitEvent(h->comm_stream, h->ev_src_ready, 0));
+    if (h->n_xev < kMaxWorld) CK(cudaEventRecord(h->ev_x0[h->n_xev], h->comm_stream));
     NK(g_nccl.AllGather(src, h->gather, h->nloc * 2, ncclDouble, h->comm, h->comm_stream));
+    if (h->n_xev < kMaxWorld) { CK(cudaEventRecord(h->ev_x1[h->n_xev], h->comm_stream)); ++h->n_xev; }
+    h->last_comm_bytes += (double)(h->world - 1) * (double)h->nloc * sizeof(double2);
     CK(cudaEventRecord(h->ev_gathered, h->comm_stream));
     h->gather_pending = true;
     for (int t = 0; t < h->world; ++t) s.p[t] = h->gather + (size_t)t * h->nloc;
@@ -157,6 +160,8 @@ static int make_slabs_needed(b200vqe_ctx *h, const double2 *src, const std::vect
     if (rc) return rc;
     CK(cudaEventRecord(h->ev_src_ready, h->stream));
     CK(cudaStreamWaitEvent(h->comm_stream, h->ev_src_ready, 0));
+    if (h->n_xev < kMaxWorld) CK(cudaEventRecord(h->ev_x0[h->n_xev], h->comm_stream));
+    h->last_comm_bytes += (double)x_ranks.size() * (double)h->nloc * sizeof(double2);
     NK(g_nccl.GroupStart());
     for (int c : x_ranks) {
         const int peer = h->rank ^ c;
@@ -165,14 +170,25 @@ static int make_slabs_needed(b200vqe_ctx *h, const double2 *src, const std::vect
         s.p[peer] = h->gather + (size_t)peer * h->nloc;
     }
     NK(g_nccl.GroupEnd());
+    if (h->n_xev < kMaxWorld) { CK(cudaEventRecord(h->ev_x1[h->n_xev], h->comm_stream)); ++h->n_xev; }
     CK(cudaEventRecord(h->ev_gathered, h->comm_stream));
     h->gather_pending = true;
     return 0;
 }
 
+// the compute stream waits for a transfer recorded in `ev`; the events around the wait time its un-hidden part
+static int wait_transfer(b200vqe_ctx *h, cudaEvent_t ev) {
+    const bool timed = h->n_wev < kMaxWorld;
+    if (timed) CK(cudaEventRecord(h->ev_w0[h->n_wev], h->stream));
+    CK(cudaStreamWaitEvent(h->stream, ev, 0));
+    if (timed) { CK(cudaEventRecord(h->ev_w1[h->n_wev], h->stream)); ++h->n_wev; }
+    return 0;
+}
+
 static int wait_gather(b200vqe_ctx *h) {
     if (!h->gather_pending) return 0;
-    CK(cudaStreamWaitEvent(h->stream, h->ev_gathered, 0));
+    int rc = wait_transfer(h, h->ev_gathered);
+    if (rc) return rc;
     h->gather_pending = false;
     return 0;
 }
@@ -291,7 +307,7 @@ static int create_common(int n_qubits, int device, int rank, int world, const ch
         cudaEventCreateWithFlags(&h->ev_src_ready, cudaEventDisableTiming);
         cudaEventCreateWithFlags(&h->ev_gathered, cudaEventDisableTiming);
         for (int i = 0; i < 2; ++i) { cudaEventCreateWithFlags(&h->ev_recv[i], cudaEventDisableTiming); cudaEventCreateWithFlags(&h->ev_free[i], cudaEventDisableTiming); }
-        for (int i = 0; i < kMaxWorld; ++i) { cudaEventCreate(&h->ev_x0[i]); cudaEventCreate(&h->ev_x1[i]); }
+        for (int i = 0; i < kMaxWorld; ++i) { cudaEventCreate(&h->ev_x0[i]); cudaEventCreate(&h->ev_x1[i]); cudaEventCreate(&h->ev_w0[i]); cudaEventCreate(&h->ev_w1[i]); }
         if (!g_nccl.load(g_err)) { delete h; return B200VQE_ECOMM; }
         ncclUniqueId u;
         memcpy(&u, id, 128);
@@ -321,7 +337,7 @@ int b200vqe_destroy(b200vqe_handle h) {
     cudaStreamSynchronize(h->stream);
     if (h->comm_stream) { cudaStreamSynchronize(h->comm_stream); cudaStreamDestroy(h->comm_stream); cudaEventDestroy(h->ev_src_ready); cudaEventDestroy(h->ev_gathered);
         for (int i = 0; i < 2; ++i) { cudaEventDestroy(h->ev_recv[i]); cudaEventDestroy(h->ev_free[i]); }
-        for (int i = 0; i < kMaxWorld; ++i) { cudaEventDestroy(h->ev_x0[i]); cudaEventDestroy(h->ev_x1[i]); } }
+        for (int i = 0; i < kMaxWorld; ++i) { cudaEventDestroy(h->ev_x0[i]); cudaEventDestroy(h->ev_x1[i]); cudaEventDestroy(h->ev_w0[i]); cudaEventDestroy(h->ev_w1[i]); } }
     for (auto p : h->slots) if (p) cudaFree(p);
     if (h->gather) cudaFree(h->gather);
     if (h->xbuf) cudaFree(h->xbuf);

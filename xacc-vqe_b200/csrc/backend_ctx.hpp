@@ -111,6 +111,8 @@ struct b200vqe_ctx {
     // NVLink exchange of the last sharded <psi|H|psi> / H psi: CUDA-event time of the transfers on the communication stream
     // (summed over the exchanges of the call) and the bytes this rank received
     cudaEvent_t ev_x0[b200vqe::kMaxWorld] = {}, ev_x1[b200vqe::kMaxWorld] = {}; int n_xev = 0; double last_comm_bytes = 0.0;
+    // ... and the time the compute stream spent WAITING for those transfers (the un-hidden part): events around every wait
+    cudaEvent_t ev_w0[b200vqe::kMaxWorld] = {}, ev_w1[b200vqe::kMaxWorld] = {}; int n_wev = 0;
     // particle-number sector (b200vqe_set_number_sector); sector_ne < 0: none
     int sector_ne = -1; bool sector_unit = true; uint64_t sector_rows[40] = {0};
     // options (string keys as in the reference's xacc::setOption map)
