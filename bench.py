@@ -497,7 +497,7 @@ def run_gpu(args):
     k_ms = ms_per_step if op == "terms" else float(np.mean(kernel_ms))     # terms: energy launch + per-term launch
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
     tile = args.engine != "stream"
-    kernel_name = (("k_tile_apply" if tile else "k_apply<8,true>") if apply_op else
+    kernel_name = (("k_tile_apply_pipe8" if tile else "k_apply<8,true>") if apply_op else
                    (("k_tile_expect_db<3>" if args.tile_bits == 11 else
                      {"auto": "k_tile_expect_pipe", "pipe": "k_tile_expect_pipe", 
                       "classic": "k_tile_expect<2,false,%d>" % args.dispatch}[args.expect_kernel])
@@ -524,7 +524,7 @@ def run_gpu(args):
                      "BATCH of xmask groups (48 B per amplitude per batch), so frac > 1 is expected") if apply_op else
                     ("achieved = ALGORITHMIC bytes 16 B x 2^n_local x G (SURVEY.md 8d) / CUDA-event time of the step's <psi|H|psi> launch(es). "
                      "The tile engine evaluates ~14 xmask groups per HBM read of the state (GF(2)-subspace tiles in shared memory), so frac > 1 "
-                     "by design; the physical bounds of the kernel are in 'dram' (bytes it really moves) and 'lsu' (shared-memory pipe)") if tile else
+                     "by design; the physical bounds of the kernel are in 'dram' (bytes it really moves), 'lsu' (shared-memory pipe) and 'fp64'") if tile else
                     ("achieved = 16 B x 2^n_local x G per step / CUDA-event time of the step's k_expect_energy launches "
                      "(one launch per xmask bucket); the pair form reads each pair once, so DRAM traffic is about half the model")}
     if tile and op == "expect" and traffic:
@@ -533,14 +533,22 @@ def run_gpu(args):
                         "n_batches": plan["expect_batches"]}
         clk_hz = float(clocks.get("sm_mhz") or 0) * 1e6
         if clk_hz > 0:
-            # LSU data-pipe wavefronts the design cannot avoid (one 128-byte wavefront per clock per SM): per tile the cp.async fill
-            # (8 per LDGSTS warp-instruction, 128 of them) and the own-amplitude reads (128 LDS.128 x 4), per generic record 64 LDS.128 x 4
-            tiles = be.n_local / 4096.0 * plan["expect_batches"]
-            wave = tiles * (128 * 8 + 128 * 4) + 0.72 * G * (be.n_local / 4096.0) * 64 * 4
+            # LSU data-pipe wavefronts the design cannot avoid (one 128-byte wavefront per clock per SM), from the LIVE plan
+            # (b200vqe_plan_costs): per tile and batch the cp.async fill (64 KB = 512 wavefronts), per view one register load of the
+            # 8 warps (128 LDS.128 x 4), per partner-reading record 64 LDS.128 x 4; fused blocks and pure records read nothing
+            costs = be.plan_costs()
+            tiles = be.n_local / 4096.0
+            wave = tiles * (plan["expect_batches"] * 512 + costs["view_loads"] * 512 + costs["partner_records"] * 256)
             roof["lsu"] = {"achieved": wave / (k_ms * 1e-3) / 1e9, "peak": n_sm * clk_hz / 1e9, "unit": "G wavefronts/s",
-                           "frac": wave / (k_ms * 1e-3) / (n_sm * clk_hz),
-                           "note": "design floor of shared-memory/LDGSTS wavefronts (~28 % of the records are pure-register: no partner read) / (SMs x sampled SM clock); "
-                                   "ncu l1tex__data_pipe_lsu_wavefronts: profiles/r2_ncu_full_k_tile_expect_pipe_400terms.txt"}
+                           "frac": wave / (k_ms * 1e-3) / (n_sm * clk_hz), "plan_costs": costs,
+                           "note": "design floor of shared-memory wavefronts of the live plan / (SMs x sampled SM clock); the kernel is bound by "
+                                   "instruction issue and LDS latency at 16 warps per SM, not by this pipe: "
+                                   "profiles/r2j_ncu_full_k_tile_expect_pipe_fused_2000terms.txt"}
+            # fp64 pipe: per xmask group and thread 16 pair-product + 8 butterfly/accumulate DP instructions (64 lanes per clock per SM)
+            dp = G * (be.n_local / 16.0) * 24.0
+            roof["fp64"] = {"achieved": dp / (k_ms * 1e-3) / 1e12, "peak": n_sm * 64 * clk_hz / 1e12, "unit": "T DP instr/s",
+                            "frac": dp / (k_ms * 1e-3) / (n_sm * 64 * clk_hz),
+                            "note": "DMUL/DFMA thread-instructions of the record bodies / (SMs x 64 fp64 lanes x sampled SM clock)"}
     if world > 1 and xch:
         x_ms = float(np.mean([v[0] for v in xch]))
         x_by = float(np.mean([v[1] for v in xch]))

@@ -122,6 +122,10 @@ int b200vqe_hamiltonian_stats(b200vqe_handle h, int64_t *n_terms, int64_t *n_gro
  * out[1] xmask groups, out[2] batches of H psi (0 until the first H psi plans them), out[3] x_rank classes of a sharded
  * <psi|H|psi>, out[4] chunk bits, out[5] tile bits. */
 int b200vqe_plan_stats(b200vqe_handle h, int64_t out[6]);
+/* Per-tile cost of that <psi|H|psi> plan, summed over its batches: out[0] register loads (one per view of a batch), out[1] fused view
+ * blocks (four xmask groups evaluated from registers alone), out[2] plain records, out[3] plain records that read partner rows from
+ * shared memory. */
+int b200vqe_plan_costs(b200vqe_handle h, int64_t out[4]);
 /* NVLink exchange of the last sharded b200vqe_expectation / b200vqe_apply_h / Lanczos step: CUDA-event time [ms] of the transfers on
  * the communication stream (summed) and the bytes this rank received.  The counterpart of the reference's only collective is the final all-reduce
  * (task/tasks/ComputeEnergyVQETask.cpp:114-126). */

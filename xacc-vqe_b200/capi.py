@@ -261,6 +261,12 @@ class Backend:
         self._ck(lib().b200vqe_plan_stats(self.h, out))
         return dict(zip(("expect_batches", "groups", "apply_batches", "expect_classes", "chunk_bits", "tile_bits"), [int(v) for v in out]))
 
+    def plan_costs(self):
+        """Per-tile cost of the <psi|H|psi> plan, summed over its batches (b200vqe_plan_costs)."""
+        out = (C.c_int64 * 4)()
+        self._ck(lib().b200vqe_plan_costs(self.h, out))
+        return dict(zip(("view_loads", "fused_blocks", "plain_records", "partner_records"), [int(v) for v in out]))
+
     def last_exchange(self):
         """(ms, bytes received by this rank) of the NVLink transfers of the last sharded <psi|H|psi> / H psi."""
         ms, by = C.c_double(), C.c_double()

@@ -21,6 +21,7 @@ struct Bucket { int h; int g_begin; int g_end; };   // h = -1: all-j form (weigh
 //   apply : identity kept,     groups ordered by xmask,  v_k = coef
 struct DeviceHam {
     int64_t n_terms = 0;            // as given by the caller
+    int64_t tile_view_loads = 0, tile_fused_blocks = 0, tile_plain_recs = 0, tile_partner_recs = 0;   // of the <psi|H|psi> plan (tile_plan.hpp)
     uint64_t fingerprint = 0;       // FNV-1a of (n, sorted (xmask, zmask, coef) table): Lanczos checkpoints are bound to it
     int64_t n_terms_nonid = 0;
     bool realc = true;

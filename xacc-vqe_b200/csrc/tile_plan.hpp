@@ -134,6 +134,9 @@ struct TilePlan {
     std::vector<uint8_t> group_view; // per group: the view its xv / its terms' z parts are expressed in (all 0 without views)
     int max_views = 1;               // largest TileBatch::n_views of the plan
     bool fused = false;              // the record stream has view markers in front of EVERY view and fused view blocks
+    // what one pass over the plan costs per tile (build_tile_records): register loads (views), fused blocks, plain records and
+    // those of them that read partner rows from shared memory
+    int64_t n_view_loads = 0, n_fused_blocks = 0, n_plain_recs = 0, n_partner_recs = 0;
 };
 
 // Which tiles (cosets) of every batch a rank of a sharded register evaluates in <psi|H|psi>: a contiguous 1/world share;
@@ -665,6 +668,7 @@ inline TilePlanOpts apply_plan_opts(int planner = 2) {
 inline void build_tile_records(TilePlan &P, bool allow_pure = false, bool fuse = false, bool apply_keys = false) {
     P.recs.clear();
     P.fused = fuse;
+    P.n_view_loads = P.n_fused_blocks = P.n_plain_recs = P.n_partner_recs = 0;
     constexpr unsigned tmask = (1u << kTileThreadBits) - 1;
     for (TileBatch &B : P.batches) {
         // fused view blocks: per view, the generator groups (xv = register bit j alone, one term)
@@ -720,6 +724,9 @@ inline void build_tile_records(TilePlan &P, bool allow_pure = false, bool fuse =
         }
         std::stable_sort(rs.begin(), rs.end(), [](const TileRec &a, const TileRec &b) { return a.view != b.view ? a.view < b.view : a.key < b.key; });
         B.r_begin = (int32_t)P.recs.size();
+        ++P.n_view_loads;                       // view 0 of the batch
+        P.n_plain_recs += (int64_t)rs.size();
+        for (const TileRec &r : rs) if (r.key < kTileRecKeys || apply_keys) ++P.n_partner_recs;
         auto open_view = [&](uint32_t v) {      // marker (+ fused block): the kernel loads its registers in the layout of view v
             TileRec m{};
             m.key = (uint8_t)kTileRecKeyView;
@@ -727,6 +734,8 @@ inline void build_tile_records(TilePlan &P, bool allow_pure = false, bool fuse =
             const bool on = fuse && blocks[v].on;
             m.count = on ? 1u + (uint32_t)blocks[v].ne : 0u;
             P.recs.push_back(m);
+            if (v) ++P.n_view_loads;
+            if (on) ++P.n_fused_blocks;
             if (!on) return;
             for (int j = 0; j < 4; ++j) {
                 TileFusedSlot fs{};
