@@ -6,6 +6,7 @@
 #include "kernels_tile.cuh"
 #include "kernels_tile_ring.cuh"
 #include "kernels_tile_apply_pipe.cuh"
+#include "kernels_rot_tile.cuh"
 #include "pauli_host.hpp"
 
 #include <algorithm>
@@ -288,6 +289,7 @@ static int create_common(int n_qubits, int device, int rank, int world, const ch
         set((const void *)k_tile_expect_pipe<false>, kPipeSmemBytes);
         set((const void *)k_tile_expect_pipe<true>, kPipeSmemBytes);
         set((const void *)k_sweep_small, tile);
+        set((const void *)k_rot_tile, tile);
         if (ea != cudaSuccess) return fail(std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(ea), B200VQE_ECUDA);
     }
     if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail(cudaGetErrorString(e), B200VQE_ECUDA);
@@ -343,6 +345,7 @@ int b200vqe_destroy(b200vqe_handle h) {
     if (h->xbuf) cudaFree(h->xbuf);
     h->ham.free_device();
     cudaFree(h->partials); cudaFree(h->counter); cudaFree(h->d_out); cudaFreeHost(h->h_out);
+    if (h->d_rot) cudaFree(h->d_rot);
     if (h->d_term_partials) cudaFree(h->d_term_partials);
     if (h->d_term_out) cudaFree(h->d_term_out);
     if (h->d_alpha) cudaFree(h->d_alpha);
@@ -390,6 +393,12 @@ int b200vqe_set_option(b200vqe_handle h, const char *key, const char *value) {
         else if (v == "tile") h->opt_expect_engine = 1;
         else if (v == "stream") h->opt_expect_engine = 2;
         else FAIL(B200VQE_EINVAL, "expect-engine must be auto, tile or stream");
+        return 0;
+    }
+    if (k == "fuse-rotations") {
+        if (v == "on" || v == "1") h->opt_fuse_rotations = 1;
+        else if (v == "off" || v == "0") h->opt_fuse_rotations = 0;
+        else FAIL(B200VQE_EINVAL, "fuse-rotations must be on or off");
         return 0;
     }
     if (k == "apply-engine") {

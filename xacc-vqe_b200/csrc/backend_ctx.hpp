@@ -104,6 +104,7 @@ struct b200vqe_ctx {
     double *d_alpha = nullptr, *d_norm = nullptr, *d_ritz = nullptr; int lanczos_cap = 0;
     // Lanczos recurrence kept between calls (resume / checkpoint): alpha_0..alpha_{m-1}, beta_1..beta_m, W_m and W_{m-1} in slots 1, 2
     std::vector<double> lz_a, lz_b; int lz_m = -1;
+    unsigned char *d_rot = nullptr; size_t rot_cap = 0; int64_t rot_runs = 0;   // tables of the fused rotation runs (kernels_rot_tile.cuh); runs launched so far
     double *d_term_partials = nullptr, *d_term_out = nullptr; size_t term_partials_cap = 0, term_out_cap = 0;
     ncclComm_t comm = nullptr;
     std::string err;
@@ -123,6 +124,7 @@ struct b200vqe_ctx {
     int opt_tile_bits = 12;             // tile of the <psi|H|psi> engine: 12 = 4096 amplitudes single-buffered, 11 = 2048 double-buffered
     int opt_shard_exchange = 0;         // tile H psi on a sharded register: 0 all-gather (auto), 1 pairwise pipeline, 2 needed slabs only (one send/recv group)
     int opt_expect_kernel = 0;          // <psi|H|psi> on 4096-amplitude tiles: 0 pipelined kernel (k_tile_expect_pipe: 3-stage cp.async ring), 1 k_tile_expect
+    int opt_fuse_rotations = 1;         // consecutive Pauli rotations with local flip masks run as fused tile passes (0: one launch per rotation)
     int opt_tile_dispatch = 1;          // record dispatch of k_tile_expect: 0 key-test chain, 1 jump table per record, 2 chain without pure-register records
     int opt_tile_planner = 3;           // tile planner version (tile_plan.hpp: 3 = 2 + several register subspaces (views) per batch, 2 = collision-greedy subspaces + sheared register subspace, 1 = first version)
     int opt_tile_chunk_bits = 3;        // C: contiguous amplitudes per chunk = 2^C (128 B at C = 3), <psi|H|psi> plans

@@ -257,6 +257,26 @@ struct KeyCounter {
 
 }  // namespace tileplan
 
+// Tile number -> coset representative.  The subspace of a batch has one pivot bit per basis vector; the representatives of
+// its cosets are the high indices with zeros at the pivots, and tile t is the representative whose remaining bits spell t:
+// tile index bits [lo_i, hi_i) move up by i = number of pivots below them (TileBatch::seg), pad[0] = the pivot mask.
+inline void set_tile_segments(TileBatch &B, const std::vector<int> &pivots) {
+    std::vector<int> sp(pivots.begin(), pivots.end());
+    std::sort(sp.begin(), sp.end());
+    const int dim = (int)sp.size();
+    int lob = 0;
+    for (int i = 0; i <= kTileMaxDim; ++i) B.seg[i] = 0;
+    for (int i = 0; i <= dim; ++i) {
+        const int hib = i < dim ? sp[i] - i : 32;
+        uint64_t m = 0;
+        if (hib > lob) m = ((hib >= 32 ? (1ull << 32) : (1ull << hib)) - 1) & ~((1ull << lob) - 1);
+        B.seg[i] = (uint32_t)m;
+        lob = hib;
+    }
+    B.pad[0] = 0;
+    for (int p : pivots) B.pad[0] |= 1u << p;
+}
+
 // terms: non-identity terms with u already set (coef or i*coef, real part).  Groups of equal x.
 inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> &in, const TilePlanOpts &o) {
     using namespace tileplan;
@@ -569,23 +589,11 @@ inline TilePlan build_tile_plan(int n, int C, const std::vector<TilePlanTermIn> 
             B.basis[i] = (uint32_t)v;
         }
         for (int k = 0; k < 4; ++k) B.lam[k] = lam[k];
-        for (int p : rr.piv) B.pad[0] |= 1u << p;      // pivot mask: the coset representative of tile t + s is ((rep | pad[0]) + deposit(s)) & ~pad[0]
         B.n_views = (uint32_t)views.size();
         P.max_views = std::max(P.max_views, (int)views.size());
         for (size_t k = 0; k < views.size(); ++k)
             for (int i = 0; i < TB; ++i) B.vcol[k][i] = (uint16_t)(view_coords(views[0], views[k].col[i]) << 4);
-        std::vector<int> sp(rr.piv.begin(), rr.piv.end());
-        std::sort(sp.begin(), sp.end());
-        {   // tile index bits [lo_i, hi_i) move up by i = number of pivots below them
-            int lob = 0;
-            for (int i = 0; i <= dim; ++i) {
-                const int hib = i < dim ? sp[i] - i : 32;
-                uint64_t m = 0;
-                if (hib > lob) m = ((hib >= 32 ? (1ull << 32) : (1ull << hib)) - 1) & ~((1ull << lob) - 1);
-                B.seg[i] = (uint32_t)m;
-                lob = hib;
-            }
-        }
+        set_tile_segments(B, rr.piv);
         B.g_begin = (int32_t)P.groups.size();
         B.t_begin = (int32_t)P.terms.size();
         // order the members by pair-selector class (hsel 0, 1, 2, 3, then -1): one code path per class on the device
