@@ -62,6 +62,24 @@ struct NcclApi {
     }
 };
 NcclApi g_nccl;
+
+// stream memory operations of the driver API (no runtime-API counterpart): the front end waits for / writes a 32-bit word, no SM
+struct CuApi {
+    void *lib = nullptr;
+    int (*WaitValue32)(cudaStream_t, unsigned long long, unsigned, unsigned) = nullptr;
+    bool tried = false;
+    bool load() {
+        if (tried) return WaitValue32 != nullptr;
+        tried = true;
+        lib = dlopen("libcuda.so.1", RTLD_NOW | RTLD_GLOBAL);
+        if (!lib) return false;
+        void *f = dlsym(lib, "cuStreamWaitValue32_v2");
+        if (!f) f = dlsym(lib, "cuStreamWaitValue32");
+        WaitValue32 = reinterpret_cast<int (*)(cudaStream_t, unsigned long long, unsigned, unsigned)>(f);
+        return WaitValue32 != nullptr;
+    }
+};
+CuApi g_cu;
 thread_local std::string g_err;
 }  // namespace
 
@@ -226,6 +244,73 @@ static int exchange_async(b200vqe_ctx *h, const double2 *src, int peer, double2 
     return 0;
 }
 
+// Peer staging for the sharded <psi|H|psi>: allocate, export through CUDA IPC, map every peer's.  COLLECTIVE (every rank of the
+// communicator must call it at the same point); the ranks agree through an all-reduce whether all of them succeeded, else all of
+// them stay on NCCL send/recv.  Returns 0 also when unavailable (h->peer_state tells).
+static int ensure_peer_staging(b200vqe_ctx *h) {
+    if (h->peer_state != 0 || h->world == 1) return 0;
+    h->peer_state = -1;
+    const size_t slab = h->nloc * sizeof(double2), bytes = 2 * slab + 4096;
+    bool ok = h->opt_peer_copy != 0 && g_cu.load();
+    if (ok && !h->h_seq && cudaMallocHost(&h->h_seq, 1024 * sizeof(unsigned)) != cudaSuccess) { cudaGetLastError(); ok = false; }
+    void *block = nullptr;
+    cudaIpcMemHandle_t mine{};
+    if (ok && cudaMalloc(&block, bytes) != cudaSuccess) { cudaGetLastError(); ok = false; block = nullptr; }
+    if (ok && cudaMemsetAsync(static_cast<char *>(block) + 2 * slab, 0, 4096, h->stream) != cudaSuccess) ok = false;
+    if (ok && cudaIpcGetMemHandle(&mine, block) != cudaSuccess) { cudaGetLastError(); ok = false; }
+    // all handles to every rank (64 bytes each), and a vote
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t size");
+    char *d_h = reinterpret_cast<char *>(h->d_out);                     // kOutDoubles * 8 = 2048 bytes >= 64 * kMaxWorld + 8
+    double vote = ok ? 1.0 : 0.0;
+    CK(cudaMemcpyAsync(d_h + 64 * h->rank, &mine, 64, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(d_h + 64 * kMaxWorld, &vote, 8, cudaMemcpyHostToDevice, h->stream));
+    NK(g_nccl.AllGather(d_h + 64 * h->rank, d_h, 64, ncclChar, h->comm, h->stream));
+    NK(g_nccl.AllReduce(d_h + 64 * kMaxWorld, d_h + 64 * kMaxWorld, 1, ncclDouble, ncclSum, h->comm, h->stream));
+    std::vector<cudaIpcMemHandle_t> all(h->world);
+    CK(cudaMemcpyAsync(all.data(), d_h, 64 * h->world, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(&vote, d_h + 64 * kMaxWorld, 8, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    bool all_ok = vote > h->world - 0.5;
+    if (all_ok) {
+        for (int p = 0; p < h->world && all_ok; ++p) {
+            if (p == h->rank) continue;
+            void *q = nullptr;
+            if (cudaIpcOpenMemHandle(&q, all[p], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); all_ok = false; break; }
+            h->peer_pbuf[p] = static_cast<double2 *>(q);
+            h->peer_pflags[p] = reinterpret_cast<unsigned *>(static_cast<char *>(q) + 2 * slab);
+        }
+    }
+    // second vote: every rank could map every peer
+    vote = all_ok ? 1.0 : 0.0;
+    CK(cudaMemcpyAsync(d_h, &vote, 8, cudaMemcpyHostToDevice, h->stream));
+    NK(g_nccl.AllReduce(d_h, d_h, 1, ncclDouble, ncclSum, h->comm, h->stream));
+    CK(cudaMemcpyAsync(&vote, d_h, 8, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    if (vote > h->world - 0.5) {
+        h->pbuf = static_cast<double2 *>(block);
+        h->pflags = reinterpret_cast<unsigned *>(static_cast<char *>(block) + 2 * slab);
+        h->peer_state = 1;
+        return 0;
+    }
+    for (int p = 0; p < h->world; ++p) if (h->peer_pbuf[p]) { cudaIpcCloseMemHandle(h->peer_pbuf[p]); h->peer_pbuf[p] = nullptr; h->peer_pflags[p] = nullptr; }
+    if (block) cudaFree(block);
+    return 0;
+}
+
+// stream `st` waits until the LOCAL flag word has reached `value` (wrap-safe >=); no SM involved
+static int flag_wait(b200vqe_ctx *h, cudaStream_t st, const unsigned *flag, unsigned value) {
+    const int r = g_cu.WaitValue32(st, (unsigned long long)(uintptr_t)flag, value, 0u /* CU_STREAM_WAIT_VALUE_GEQ */);
+    if (r != 0) FAIL(B200VQE_ECUDA, "cuStreamWaitValue32 failed (" + std::to_string(r) + ")");
+    return 0;
+}
+// stream `st` sets a flag word in a PEER's memory: a 4-byte copy from a pinned ring (copy engine, no SM)
+static int flag_push(b200vqe_ctx *h, cudaStream_t st, unsigned *remote_flag, unsigned value) {
+    unsigned *src = h->h_seq + (h->h_seq_pos++ & 1023u);
+    *src = value;
+    CK(cudaMemcpyAsync(remote_flag, src, sizeof(unsigned), cudaMemcpyDefault, st));
+    return 0;
+}
+
 static int allreduce_doubles(b200vqe_ctx *h, double *dptr, size_t count) {
     if (h->world == 1) return 0;
     NK(g_nccl.AllReduce(dptr, dptr, count, ncclDouble, ncclSum, h->comm, h->stream));
@@ -343,6 +428,9 @@ int b200vqe_destroy(b200vqe_handle h) {
     for (auto p : h->slots) if (p) cudaFree(p);
     if (h->gather) cudaFree(h->gather);
     if (h->xbuf) cudaFree(h->xbuf);
+    for (int p = 0; p < kMaxWorld; ++p) if (h->peer_pbuf[p]) cudaIpcCloseMemHandle(h->peer_pbuf[p]);
+    if (h->pbuf) cudaFree(h->pbuf);
+    if (h->h_seq) cudaFreeHost(h->h_seq);
     h->ham.free_device();
     cudaFree(h->partials); cudaFree(h->counter); cudaFree(h->d_out); cudaFreeHost(h->h_out);
     if (h->d_rot) cudaFree(h->d_rot);
@@ -393,6 +481,13 @@ int b200vqe_set_option(b200vqe_handle h, const char *key, const char *value) {
         else if (v == "tile") h->opt_expect_engine = 1;
         else if (v == "stream") h->opt_expect_engine = 2;
         else FAIL(B200VQE_EINVAL, "expect-engine must be auto, tile or stream");
+        return 0;
+    }
+    if (k == "peer-copy") {
+        if (v == "on" || v == "1") h->opt_peer_copy = 1;
+        else if (v == "off" || v == "0") h->opt_peer_copy = 0;
+        else FAIL(B200VQE_EINVAL, "peer-copy must be on or off");
+        if (h->peer_state != 0) FAIL(B200VQE_EINVAL, "peer-copy must be set before the first sharded <psi|H|psi>");
         return 0;
     }
     if (k == "fuse-rotations") {

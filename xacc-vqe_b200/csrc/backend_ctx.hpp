@@ -97,6 +97,16 @@ struct b200vqe_ctx {
     std::vector<double2 *> slots;
     double2 *gather = nullptr;          // [world][nloc] staging of the peers' shards
     double2 *xbuf = nullptr;            // [2][nloc] staging of peer shards (pairwise exchanges: ansatz gates, tile H psi) when gather is absent
+    // Peer staging (sharded <psi|H|psi>): two slabs + flag words in ONE allocation that every peer maps through CUDA IPC; a peer PUSHES
+    // its slab into it with a device-to-device copy (copy engine over NVLink) and raises arrived[b] with a 4-byte copy; this rank tells
+    // every peer with 4-byte copies when the class that read buffer b is done.  All waits are stream memory operations on LOCAL flag
+    // words (cuStreamWaitValue32): nothing here needs an SM -- the persistent tile kernels hold every register of every SM, so NCCL's
+    // send/recv kernels (and any flag kernel) only run when a tile kernel ends.
+    double2 *pbuf = nullptr; unsigned *pflags = nullptr;              // flags: [0,1] arrived[b]; [4 + 2 p + b] free_from[p][b]: peer p is done with ITS buffer b
+    unsigned *h_seq = nullptr; unsigned h_seq_pos = 0;                 // pinned ring of sequence numbers: sources of the 4-byte flag copies
+    double2 *peer_pbuf[b200vqe::kMaxWorld] = {}; unsigned *peer_pflags[b200vqe::kMaxWorld] = {};
+    int peer_state = 0;                                                // 0 not tried, 1 ready, -1 unavailable (NCCL send/recv instead)
+    unsigned xseq = 0, buf_last_seq[2] = {0, 0};                       // exchange sequence numbers (identical on every rank)
     cudaEvent_t ev_recv[2] = {nullptr, nullptr}, ev_free[2] = {nullptr, nullptr};   // pipelined slab exchange of the tile H psi
     b200vqe::DeviceHam ham;
     double *partials = nullptr; unsigned *counter = nullptr;
@@ -124,6 +134,7 @@ struct b200vqe_ctx {
     int opt_tile_bits = 12;             // tile of the <psi|H|psi> engine: 12 = 4096 amplitudes single-buffered, 11 = 2048 double-buffered
     int opt_shard_exchange = 0;         // tile H psi on a sharded register: 0 all-gather (auto), 1 pairwise pipeline, 2 needed slabs only (one send/recv group)
     int opt_expect_kernel = 0;          // <psi|H|psi> on 4096-amplitude tiles: 0 pipelined kernel (k_tile_expect_pipe: 3-stage cp.async ring), 1 k_tile_expect
+    int opt_peer_copy = 1;              // sharded <psi|H|psi>: 1 slab swaps as peer-memory copies (CUDA IPC + copy engine), 0 NCCL send/recv
     int opt_fuse_rotations = 1;         // consecutive Pauli rotations with local flip masks run as fused tile passes (0: one launch per rotation)
     int opt_tile_dispatch = 1;          // record dispatch of k_tile_expect: 0 key-test chain, 1 jump table per record, 2 chain without pure-register records
     int opt_tile_planner = 3;           // tile planner version (tile_plan.hpp: 3 = 2 + several register subspaces (views) per batch, 2 = collision-greedy subspaces + sheared register subspace, 1 = first version)
