@@ -101,12 +101,21 @@ const char *b200vqe_last_error(b200vqe_handle h);
  *                                                    slabs: one ncclAllGather into `world` staging slabs (auto; fastest measured) |
  *                                                    only the slabs the Hamiltonian's masks reach, one group of ncclSend/ncclRecv |
  *                                                    per-x_rank send/recv pairs pipelined through two staging slabs (least memory)
- *   "tile-bits"       = "12" | "11"                  tile of the <psi|H|psi> engine: 4096 amplitudes single-buffered (two CTAs
- *                                                    per SM) | 2048 amplitudes double-buffered with cp.async (three CTAs per SM)
- *   "tile-ctas-per-sm" = "2" | "3"                   resident CTAs per SM of the tile engine's <psi|H|psi> kernel
- *   "tile-chunk-bits" = "2".."8"                     contiguous amplitudes per HBM chunk of the tile engine
- *   "tile-planner"    = "2" | "1"                    tile planner: collision-greedy subspaces + register subspace spanned by
- *                                                    member masks (pure-register records) | the first version
+ *   "expect-kernel"   = "auto" | "pipe" | "classic"  <psi|H|psi> on 4096-amplitude tiles: the pipelined kernel (3-stage cp.async ring,
+ *                                                    views, fused view blocks; default) | the single-buffer kernel of round 1
+ *   "tile-bits"       = "12" | "11"                  tile of the <psi|H|psi> engine: 4096 amplitudes | 2048 amplitudes double-buffered
+ *                                                    with cp.async (three CTAs per SM; k_tile_expect_db)
+ *   "tile-ctas-per-sm" = "2" | "3"                   resident CTAs per SM of the single-buffer <psi|H|psi> kernel
+ *   "tile-dispatch"   = "0".."3"                     record dispatch of the single-buffer kernel (A/B variants of round 2)
+ *   "tile-chunk-bits" = "2".."8"                     contiguous amplitudes per HBM chunk of the tile engine (default 3: 128 bytes);
+ *   "apply-chunk-bits"                               the same for the H psi plans alone (default 4: 256 bytes)
+ *   "tile-planner"    = "3" | "2" | "1"              tile planner: 2 + several register subspaces (views) per batch and fused view
+ *                                                    blocks (default; walked by the pipelined kernel only) | collision-greedy
+ *                                                    subspaces + register subspace spanned by member masks | the first version
+ *   "fuse-rotations"  = "on" | "off"                 b200vqe_apply_pauli_rotations: consecutive rotations with local flip masks run as
+ *                                                    fused tile passes (one HBM pass per run) | one launch per rotation
+ *   "peer-copy"       = "on" | "off"                 sharded <psi|H|psi>: slab swaps as peer-memory copies (CUDA IPC + copy engine,
+ *                                                    no SM) | grouped ncclSend/ncclRecv; set before the first sharded expectation
  * Options take effect at the next b200vqe_set_hamiltonian. */
 int b200vqe_set_option(b200vqe_handle h, const char *key, const char *value);
 int b200vqe_n_slots(b200vqe_handle h, int n_slots);   /* number of resident statevectors (default 1) */
@@ -140,7 +149,7 @@ int b200vqe_debug_tile_plan(int n_qubits, int chunk_bits, int tile_bits /* 12 | 
                             const double *coef_re, const double *coef_im, int64_t *n_batches, int64_t *n_groups,
                             int64_t *n_plan_terms, void *batches, void *groups, void *terms);
 
-/* Host-only: planner version (the "tile-planner" option) the b200vqe_debug_* plan functions use; default 2. */
+/* Host-only: planner version (the "tile-planner" option) the b200vqe_debug_* plan functions use; default 3. */
 int b200vqe_debug_set_planner(int planner);
 
 /* Host-only: the TileRec[32 B] records (csrc/tile_plan.hpp) the <psi|H|psi> kernel walks for that plan; the r_begin / r_end

@@ -103,6 +103,46 @@ def config3():
     be.close()
 
 
+def faithful_baseline():
+    """BASELINE.md section 4, "B-faithful": the reference's own way -- string-based row builder (DiagonalizeTask.cpp:189-203) +
+    dense Hermitian solve (:205), ONE thread, as the reference is -- timed on this box's host for configs 1-3 beside the device
+    numbers above.  Config 3's 2^14 x 2^14 dense matrix (4.3 GB, ~4e12 flops x c to diagonalise) is not formed: the row builder is
+    timed on a bounded block of rows and scaled, the dense solve is reported as not run."""
+    from threadpoolctl import threadpool_limits
+    golden = json.load(open(os.path.join(ROOT, "tests", "golden", "reference_fixtures.json")))
+    out = {"baseline": "B-faithful: string-based dense build + dense eigen-solve, 1 thread (oracle/hpsi_oracle.c oracle_faithful_*)",
+           "host_cores": os.cpu_count(), "threads_used": 1}
+    with threadpool_limits(limits=1):
+        # config 1: H2, 4 qubits
+        op, n = po.compile_fermion_source(golden["h2_source"], "jw")
+        t0 = time.perf_counter()
+        for _ in range(200):
+            A = co.faithful_dense(op, n)
+            w = np.linalg.eigvalsh(A)
+        out["config1_h2_4q"] = {"ms_per_diagonalize": 1e3 * (time.perf_counter() - t0) / 200, "E0": float(w[0])}
+        # config 2: 12-qubit BK molecule-shaped operator
+        op, n = po.compile_fermion_source(lih_shaped_source(12, seed=12), "bk", 12)
+        t0 = time.perf_counter()
+        A = co.faithful_dense(op, n)
+        t_build = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        w = np.linalg.eigvalsh(A)
+        t_eig = time.perf_counter() - t0
+        out["config2_12q_bk"] = {"n_terms": len(op), "dense_build_s": t_build, "dense_eigensolve_s": t_eig, "E0": float(w[0])}
+        del A
+        # config 3: 14-qubit JW molecule-shaped operator: 512 of the 16384 rows of the row builder
+        op, n = po.compile_fermion_source(lih_shaped_source(14, seed=14), "jw", 14)
+        psi = np.random.default_rng(0).normal(size=1 << n) + 0j
+        rows = 512
+        t0 = time.perf_counter()
+        co.faithful_apply_rows(op, n, psi, 0, rows)
+        dt = time.perf_counter() - t0
+        out["config3_14q_jw"] = {"n_terms": len(op), "row_builder_s_for_%d_rows" % rows: dt, "row_builder_s_scaled_to_all_rows": dt * (1 << n) / rows,
+                                 "dense_eigensolve": "not run: 16384 x 16384 complex (4.3 GB), O(N^3)"}
+    print(json.dumps(out))
+
+
 if __name__ == "__main__":
     config1()
     config3()
+    faithful_baseline()
