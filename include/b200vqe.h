@@ -180,6 +180,8 @@ int b200vqe_debug_shard_layout(int n_qubits, int rank, int world, int tile_bits,
 int b200vqe_state_reset(b200vqe_handle h, int slot, uint64_t basis_index);
 int b200vqe_state_upload(b200vqe_handle h, int slot, const double *amps, uint64_t first, uint64_t count);
 int b200vqe_state_download(b200vqe_handle h, int slot, double *amps, uint64_t first, uint64_t count, int order);
+        /* order = B200VQE_ORDER_REFERENCE: whole local range only; on a sharded handle the call is collective and rank r
+         * receives the reference indices [r 2^nl, (r + 1) 2^nl) (the register is gathered once: `world` staging slabs) */
 int b200vqe_state_random(b200vqe_handle h, int slot, uint64_t seed);            /* normalised complex Gaussian */
 int b200vqe_state_product(b200vqe_handle h, int slot, const double *a, const double *b);
                         /* (x)_q (cos a_q |0> + e^{i b_q} sin a_q |1>) */

@@ -37,6 +37,10 @@ def _worker(rank, world, comm_id, n, T, seed, engine, lanczos, out_q):
     lo, cnt = be.first, be.n_local
     be.upload(psi[lo:lo + cnt])
     e, per = be.expectation(per_term=True)
+    # the energy alone takes the capacity-scaling path: x_rank classes over pair registers, slab swaps as peer-memory pushes
+    # (twice: the second call reuses the staging buffers and their flag words)
+    e_only = [be.expectation(), be.expectation()]
+    ref_part = be.download(0, order=xb.capi.ORDER_REFERENCE)       # collective: this rank's range of the reference index order
     alpha = be.apply_h(0, 1)
     hpsi = be.download(1)
     nrm = be.norm2(0)
@@ -44,7 +48,7 @@ def _worker(rank, world, comm_id, n, T, seed, engine, lanczos, out_q):
     if lanczos:
         e0, it, res = be.lanczos_ground(tol=1e-10, max_iter=3000, seed=seed, want_vector=True)
         vec = be.download(0)
-    out_q.put((rank, e, per, alpha, lo, hpsi, nrm, e0, vec))
+    out_q.put((rank, e, per, alpha, lo, hpsi, nrm, e0, vec, e_only, ref_part))
     be.close()
 
 
@@ -77,8 +81,13 @@ def test_shards_match_oracle(n, T, seed, engine, lanczos, world):
     ref = co.apply(n, xm, zm, cf, psi)
     full = np.zeros(1 << n, complex)
     vec = np.zeros(1 << n, complex)
-    for rank, e, per, alpha, lo, hpsi, nrm, e0, v in res:
+    # reference order: qubit q <-> bit n-1-q (DiagonalizeTask.cpp:189-193)
+    rev = np.array([int(format(i, "0%db" % n)[::-1], 2) for i in range(1 << n)])
+    psi_ref = psi[rev]
+    for rank, e, per, alpha, lo, hpsi, nrm, e0, v, e_only, ref_part in res:
         assert abs(e - eo) < 1e-10 * scale
+        assert max(abs(x - eo) for x in e_only) < 1e-10 * scale and e_only[0] == e_only[1]
+        assert np.array_equal(ref_part, psi_ref[lo:lo + len(ref_part)])
         assert np.abs(per - pero.real).max() < 1e-11
         assert abs(alpha - np.vdot(psi, ref)) < 1e-10 * scale
         assert abs(nrm - 1.0) < 1e-12

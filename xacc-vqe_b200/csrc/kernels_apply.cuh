@@ -166,6 +166,14 @@ k_lanczos_update(double2 *__restrict__ w, const double2 *__restrict__ v, double2
 
 __global__ void k_sqrt_inplace(double *v) { *v = sqrt(*v); }
 
+// out[k] = full[bit-reversal over n bits of (first + k)]: the register in the reference's index order (qubit q <-> bit n-1-q,
+// task/tasks/DiagonalizeTask.cpp:189-193); `full` = the whole register in device order (sharded: the gathered slabs)
+__global__ void __launch_bounds__(kBlock, 4)
+k_extract_reference(const double2 *__restrict__ full, double2 *__restrict__ out, int n, uint64_t first, uint64_t count) {
+    for (uint64_t k = (uint64_t)blockIdx.x * kBlock + threadIdx.x; k < count; k += (uint64_t)gridDim.x * kBlock)
+        out[k] = full[__brevll(first + k) >> (64 - n)];
+}
+
 __global__ void __launch_bounds__(kBlock, 4)
 k_scale(double2 *__restrict__ v, uint64_t n, double s) {
     for (uint64_t j = (uint64_t)blockIdx.x * kBlock + threadIdx.x; j < n; j += (uint64_t)gridDim.x * kBlock) {

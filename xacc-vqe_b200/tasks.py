@@ -252,7 +252,7 @@ class DiagonalizeTask:
         self.iterations, self.residual = it, res
         if self.want_vector:
             # element order of the reference's eigenvector (DiagonalizeTask.cpp:189-193, :222-225)
-            self.ground_state = be.download(0, order=capi.ORDER_REFERENCE) if be.world == 1 else be.download(0)
+            self.ground_state = be.download(0, order=capi.ORDER_REFERENCE)      # sharded: this rank's range of the reference order
         if self.buffer is not None:
             self.buffer.addExtraInfo("vqe-energy", e0)
         return VQETaskResult(energy=e0, angles=np.asarray(parameters, float), vqeIterations=it)
