@@ -303,9 +303,7 @@ def run_gpu(args):
     if args.apply_chunk_bits is not None:
         be.set_option("apply-chunk-bits", args.apply_chunk_bits)
     be.set_option("tile-bits", args.tile_bits)
-    be.set_option("tile-ctas-per-sm", args.tile_ctas)
     be.set_option("tile-planner", args.planner)
-    be.set_option("tile-dispatch", args.dispatch)
     be.set_option("expect-kernel", args.expect_kernel)
     t0 = time.perf_counter()
     be.set_hamiltonian(xm, zm, cf)
@@ -500,7 +498,7 @@ def run_gpu(args):
     kernel_name = (("k_tile_apply_pipe8" if tile else "k_apply<8,true>") if apply_op else
                    (("k_tile_expect_db<3>" if args.tile_bits == 11 else
                      {"auto": "k_tile_expect_pipe", "pipe": "k_tile_expect_pipe", 
-                      "classic": "k_tile_expect<2,false,%d>" % args.dispatch}[args.expect_kernel])
+                      "classic": "k_tile_expect<2,false>"}[args.expect_kernel])
                     if tile else "k_expect_energy<8,true>"))
     # DRAM traffic of the step: the tile engine streams this rank's amplitudes once per batch (pair registers: the peer slab too),
     # modelled from the LIVE plan; the ncu capture of the same launch (profiles/traffic.json) is quoted when it matches the plan
@@ -622,10 +620,8 @@ def main():
     ap.add_argument("--no-shard-check", action="store_true", help="N > 1: skip the small sharded parity check")
     ap.add_argument("--op", default="expect", choices=["expect", "apply", "terms"], help="expect: <psi|H|psi> (headline); apply: dst = H psi; terms: <psi|H|psi> plus every <P_k>")
     ap.add_argument("--engine", default="auto", choices=["auto", "tile", "stream"], help="<psi|H|psi> kernel family")
-    ap.add_argument("--tile-ctas", type=int, default=2, choices=[2, 3], help="tile engine: resident CTAs per SM")
     ap.add_argument("--tile-bits", type=int, default=12, choices=[11, 12], help="tile engine: 12 = 4096-amplitude tiles, 11 = 2048 double-buffered")
     ap.add_argument("--expect-kernel", default="auto", choices=["auto", "pipe", "classic"])
-    ap.add_argument("--dispatch", type=int, default=1, choices=[0, 1, 2, 3])
     ap.add_argument("--planner", type=int, default=3, choices=[1, 2, 3], help="tile planner version (csrc/tile_plan.hpp)")
     ap.add_argument("--chunk-bits", type=int, default=None, help="tile engine: log2 contiguous amplitudes per HBM chunk (library default: 3 for <psi|H|psi>, 4 for H psi)")
     ap.add_argument("--apply-chunk-bits", type=int, default=None, help="the same for the H psi plans only")

@@ -105,8 +105,6 @@ const char *b200vqe_last_error(b200vqe_handle h);
  *                                                    views, fused view blocks; default) | the single-buffer kernel of round 1
  *   "tile-bits"       = "12" | "11"                  tile of the <psi|H|psi> engine: 4096 amplitudes | 2048 amplitudes double-buffered
  *                                                    with cp.async (three CTAs per SM; k_tile_expect_db)
- *   "tile-ctas-per-sm" = "2" | "3"                   resident CTAs per SM of the single-buffer <psi|H|psi> kernel
- *   "tile-dispatch"   = "0".."3"                     record dispatch of the single-buffer kernel (A/B variants of round 2)
  *   "tile-chunk-bits" = "2".."8"                     contiguous amplitudes per HBM chunk of the tile engine (default 3: 128 bytes);
  *   "apply-chunk-bits"                               the same for the H psi plans alone (default 4: 256 bytes)
  *   "tile-planner"    = "3" | "2" | "1"              tile planner: 2 + several register subspaces (views) per batch and fused view

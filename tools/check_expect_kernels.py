@@ -22,16 +22,15 @@ psi /= np.linalg.norm(psi)
 eo, _ = co.expect(n, xm, zm, cf, psi)
 scale = np.abs(cf).sum()
 ok = True
-for kern, planner, disp in (("pipe", 3, 1), ("pipe", 2, 1), ("pipe", 1, 1), ("classic", 2, 1), ("classic", 2, 0), ("classic", 1, 3)):
+for kern, planner in (("pipe", 3), ("pipe", 2), ("pipe", 1), ("classic", 2), ("classic", 1)):
     be = xb.Backend(n, device=0)
     be.set_option("expect-kernel", kern)
     be.set_option("tile-planner", planner)
-    be.set_option("tile-dispatch", disp)
     be.set_hamiltonian(xm, zm, cf)
     be.upload(psi)
     e = be.expectation()
     err = abs(e - eo) / scale
-    print(f"{kern:8s} planner {planner} dispatch {disp}: E = {e.real:+.15f}  |dE|/sum|c| = {err:.2e}  {be.last_kernel_ms():.3f} ms", flush=True)
+    print(f"{kern:8s} planner {planner}: E = {e.real:+.15f}  |dE|/sum|c| = {err:.2e}  {be.last_kernel_ms():.3f} ms", flush=True)
     ok &= err < 1e-12
     del be
 print("OK" if ok else "MISMATCH")

@@ -363,11 +363,7 @@ static int create_common(int n_qubits, int device, int rank, int world, const ch
         cudaError_t ea = cudaSuccess;
         auto set = [&](const void *f, int bytes) { if (ea == cudaSuccess) ea = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes); };
         set((const void *)k_tile_expect<2, false>, tile);
-        set((const void *)k_tile_expect<2, false, 1>, tile);
-        set((const void *)k_tile_expect<2, false, 2>, tile);
-        set((const void *)k_tile_expect<2, false, 3>, tile);
-        set((const void *)k_tile_expect<3, false, 1>, tile);
-        set((const void *)k_tile_expect<2, true, 1>, tile);
+        set((const void *)k_tile_expect<2, true>, tile);
         set((const void *)k_tile_expect_db<3>, two_small);
         set((const void *)k_tile_apply_pipe8<false>, kApply8SmemBytes);
         set((const void *)k_tile_apply_pipe8<true>, kApply8SmemBytes);
@@ -535,22 +531,10 @@ int b200vqe_set_option(b200vqe_handle h, const char *key, const char *value) {
         else FAIL(B200VQE_EINVAL, "expect-kernel must be auto, pipe or classic");
         return 0;
     }
-    if (k == "tile-dispatch") {
-        const int c = atoi(value);
-        if (c < 0 || c > 3) FAIL(B200VQE_EINVAL, "tile-dispatch must be 0..3");
-        h->opt_tile_dispatch = c;
-        return 0;
-    }
     if (k == "tile-planner") {
         const int c = atoi(value);
         if (c < 1 || c > 3) FAIL(B200VQE_EINVAL, "tile-planner must be 1, 2 or 3");
         h->opt_tile_planner = c;
-        return 0;
-    }
-    if (k == "tile-ctas-per-sm") {
-        const int c = atoi(value);
-        if (c != 2 && c != 3) FAIL(B200VQE_EINVAL, "tile-ctas-per-sm must be 2 or 3");
-        h->opt_tile_ctas = c;
         return 0;
     }
     FAIL(B200VQE_EINVAL, "unknown option '" + k + "'");

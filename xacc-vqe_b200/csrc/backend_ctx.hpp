@@ -130,13 +130,11 @@ struct b200vqe_ctx {
     // options (string keys as in the reference's xacc::setOption map)
     int opt_expect_engine = 0;          // 0 auto, 1 tile engine, 2 streaming kernel
     int opt_apply_engine = 0;           // same, for H psi
-    int opt_tile_ctas = 2;              // resident CTAs per SM of the tile engine (2 or 3)
     int opt_tile_bits = 12;             // tile of the <psi|H|psi> engine: 12 = 4096 amplitudes single-buffered, 11 = 2048 double-buffered
     int opt_shard_exchange = 0;         // tile H psi on a sharded register: 0 all-gather (auto), 1 pairwise pipeline, 2 needed slabs only (one send/recv group)
     int opt_expect_kernel = 0;          // <psi|H|psi> on 4096-amplitude tiles: 0 pipelined kernel (k_tile_expect_pipe: 3-stage cp.async ring), 1 k_tile_expect
     int opt_peer_copy = 1;              // sharded <psi|H|psi>: 1 slab swaps as peer-memory copies (CUDA IPC + copy engine), 0 NCCL send/recv
     int opt_fuse_rotations = 1;         // consecutive Pauli rotations with local flip masks run as fused tile passes (0: one launch per rotation)
-    int opt_tile_dispatch = 1;          // record dispatch of k_tile_expect: 0 key-test chain, 1 jump table per record, 2 chain without pure-register records
     int opt_tile_planner = 3;           // tile planner version (tile_plan.hpp: 3 = 2 + several register subspaces (views) per batch, 2 = collision-greedy subspaces + sheared register subspace, 1 = first version)
     int opt_tile_chunk_bits = 3;        // C: contiguous amplitudes per chunk = 2^C (128 B at C = 3), <psi|H|psi> plans
     int opt_apply_chunk_bits = 4;       // the same for H psi plans: 256-byte chunks make the dst read-modify-write stream measurably faster

@@ -10,7 +10,7 @@
 // thread part) and a Walsh function of r: one 8-point signed butterfly (7 DFMA) per term on top of the record's
 // Re w / Im w products.
 //
-// Kernels: k_tile_expect<MINB, PT> (single buffer; PT = per-term sums instead of the energy), k_tile_expect_db<3>
+// Kernels: k_tile_expect<2, PT> (single buffer; PT = per-term sums instead of the energy), k_tile_expect_db<3>
 // (2048-amplitude tiles, cp.async double buffering, opt-in), k_sum_term_partials; H psi: kernels_tile_apply_pipe.cuh.
 // HBM traffic of <psi|H|psi>: 16 B per amplitude per BATCH (>= kTileBits - C groups), no writes.
 #pragma once
@@ -220,36 +220,6 @@ __device__ __forceinline__ void tile_one(const double2 (&a)[1 << RB], const doub
     }
 }
 
-// one dispatch per RUN of equal keys (the records of a batch are sorted by key)
-template <int RB>
-__device__ __forceinline__ void tile_walk_runs(const double2 (&a)[1 << RB], const double2 *__restrict__ tile, unsigned v0, unsigned rep,
-                                               const int4 *__restrict__ s_recs, const double2 *__restrict__ s_terms, double &acc) {
-    int gi = 0;
-    int4 ra = s_recs[0], rb = s_recs[1];
-#pragma unroll 1
-    for (;;) {
-        const unsigned key = (unsigned)ra.z >> 16;
-        if (key >= 2u * kTileRecKeys) break;                          // sentinel
-#define B200VQE_CASE(K)                                                                        \
-        case K:                                                                                \
-            do {                                                                               \
-                const int4 ca = ra, cb = rb;                                                   \
-                ++gi;                                                                          \
-                ra = s_recs[2 * gi];                                                           \
-                rb = s_recs[2 * gi + 1];                                                       \
-                tile_one<RB, K, false>(a, tile, v0, rep, ca, cb, s_terms, acc, nullptr);       \
-            } while (((unsigned)ra.z >> 16) == (unsigned)(K));                                 \
-            break;
-#define B200VQE_CASE8(K) B200VQE_CASE(K) B200VQE_CASE(K + 1) B200VQE_CASE(K + 2) B200VQE_CASE(K + 3) B200VQE_CASE(K + 4) B200VQE_CASE(K + 5) B200VQE_CASE(K + 6) B200VQE_CASE(K + 7)
-        switch (key) {
-            B200VQE_CASE8(0) B200VQE_CASE8(8) B200VQE_CASE8(16) B200VQE_CASE8(24) B200VQE_CASE8(32) B200VQE_CASE8(40) B200VQE_CASE8(48) B200VQE_CASE8(56)
-            default: break;
-        }
-#undef B200VQE_CASE8
-#undef B200VQE_CASE
-    }
-}
-
 template <int RB, bool PT = false>
 __device__ __forceinline__ void tile_switch(const double2 (&a)[1 << RB], const double2 *__restrict__ tile, unsigned v0, unsigned rep,
                                             const int4 *__restrict__ s_recs, const double2 *__restrict__ s_terms, int n_r, double &acc,
@@ -286,10 +256,11 @@ __device__ __forceinline__ void prefetch_l2(const void *p) {
 // PT = per-term output (b200vqe_expectation(per_term), RDM): instead of the energy, every CTA leaves the signed pair
 // sums of each term over ITS tiles in term_partials[blockIdx.x][plan term] (per-warp accumulators in shared memory,
 // flushed at every batch switch; fixed order, no atomics); k_sum_term_partials adds the CTAs in order.
-// DISP = how the records of a batch are dispatched to their specialised loops: 0 chain of key tests over all 64 keys,
-// 1 one jump table per record, 2 chain over the 32 generic keys only (plans without pure records), 3 = 2 without the shear
-// (planner 1 only: the kernel of the first version, kept for A/B measurements)
-template <int MINB, bool PT = false, int DISP = 0>
+// Records are dispatched to their specialised bodies by one switch per record (tile_switch).  Round 2 measured the alternatives
+// on 28 q / 10^4 terms (profiles/r2_expect_kernel_variants_28q_1e4terms.txt): a chain of key tests over all 64 keys +38 %
+// (its 64 test sites are spread over 139 KB of code), three CTAs per SM (80 registers, spills) and the unsheared planner-1
+// kernel slower as well; they are no longer built.
+template <int MINB, bool PT = false>
 __global__ void __launch_bounds__(kBlock, MINB)
 k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_bytes, const TileBatch *__restrict__ batches, int n_batches,
               unsigned long long tile_begin, unsigned long long tile_count, const TileRec *__restrict__ recs,
@@ -366,7 +337,7 @@ k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_byte
         for (int r = 0; r < 16; ++r) {
             const unsigned hi = base ^ ((r & 1) ? rb0 : 0u) ^ ((r & 2) ? rb1 : 0u) ^ ((r & 4) ? rb2 : 0u) ^ ((r & 8) ? rb3 : 0u);
             // register r holds the amplitude with low index bits lo ^ Lambda(r): still one 128-byte line per 8 lanes
-            const unsigned lor = DISP == 3 ? lo_b : (lo_b ^ ((r & 1) ? lm0 : 0u) ^ ((r & 2) ? lm1 : 0u) ^ ((r & 4) ? lm2 : 0u) ^ ((r & 8) ? lm3 : 0u));
+            const unsigned lor = lo_b ^ ((r & 1) ? lm0 : 0u) ^ ((r & 2) ? lm1 : 0u) ^ ((r & 4) ? lm2 : 0u) ^ ((r & 8) ? lm3 : 0u);
             // pair register of a sharded register (sel_mask != 0): chunks with that high-index bit set live in the peer's slab
             const char *slab = (hi & sel_mask) ? reinterpret_cast<const char *>(psi_hi) : psi_b;
             a[r] = __ldcs(reinterpret_cast<const double2 *>(slab + ((unsigned long long)(hi & ~sel_mask) * chunk_bytes + lor)));   // streamed once per batch
@@ -386,13 +357,7 @@ k_tile_expect(const double2 *__restrict__ psi, int C, int M, unsigned chunk_byte
                 prefetch_l2(((h1 & sel_mask) ? hi_lo : psi_lo) + (unsigned long long)(h1 & ~sel_mask) * chunk_bytes);
             }
         }
-        if constexpr (DISP == 1) {
-            tile_switch<4, PT>(a, tile, v0, rep, s_recs, s_terms, sb.r_end - sb.r_begin, acc, part);
-        } else {
-            int gi = 0;
-            int4 ra = s_recs[0], rb = s_recs[1];
-            tile_runs<4, 0, PT, DISP >= 2 ? kTileRecKeys : 2 * kTileRecKeys>(a, tile, v0, rep, s_recs, s_terms, gi, ra, rb, acc, part);
-        }
+        tile_switch<4, PT>(a, tile, v0, rep, s_recs, s_terms, sb.r_end - sb.r_begin, acc, part);
     }
     if (PT) {
         if (cur_b >= 0) flush_terms();
