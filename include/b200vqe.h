@@ -147,6 +147,11 @@ int b200vqe_debug_tile_plan(int n_qubits, int chunk_bits, int tile_bits /* 12 | 
                             const double *coef_re, const double *coef_im, int64_t *n_batches, int64_t *n_groups,
                             int64_t *n_plan_terms, void *batches, void *groups, void *terms);
 
+/* Host-only: the fused runs of b200vqe_apply_pauli_rotations for `count` rotations with local flip masks on one GPU: TileBatch[320 B]
+ * per run and RotRec[48 B] per rotation with phi != 0 (csrc/kernels_rot_tile.cuh); two-call pattern (NULL arrays: sizes only). */
+int b200vqe_debug_rotation_runs(int n_qubits, int64_t count, const uint64_t *xmask, const uint64_t *zmask, const double *phi,
+                                int64_t *n_runs, int64_t *n_records, void *batches, void *records);
+
 /* Host-only: planner version (the "tile-planner" option) the b200vqe_debug_* plan functions use; default 3. */
 int b200vqe_debug_set_planner(int planner);
 

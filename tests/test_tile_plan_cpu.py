@@ -487,3 +487,95 @@ def test_plan_batches_many_groups_for_structured_masks():
     zm = np.zeros(len(xm), np.uint64)
     B, G, _ = get_plan(n, 3, xm, zm, np.ones(len(xm), complex))
     assert len(G) == len(xm) and len(B) <= 2
+
+
+ROT_DT = np.dtype([("zl", "<u4"), ("xv", "<u2"), ("zv", "<u2"), ("hb", "<u4"), ("flip", "<u4"), ("c", "<f8"), ("mre", "<f8"), ("mim", "<f8"),
+                   ("pad", "<u8")])          # RotRec (csrc/kernels_rot_tile.cuh)
+
+
+def get_rotation_runs(n, xm, zm, phi):
+    lib = xb.capi.lib()
+    xm, zm = np.ascontiguousarray(xm, np.uint64), np.ascontiguousarray(zm, np.uint64)
+    phi = np.ascontiguousarray(phi, np.float64)
+    nb, nr = C.c_int64(), C.c_int64()
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)
+    args = (C.c_int(n), C.c_int64(len(xm)), vp(xm), vp(zm), vp(phi), C.byref(nb), C.byref(nr))
+    assert lib.b200vqe_debug_rotation_runs(*args, None, None) == 0
+    B, R = np.zeros(nb.value, BATCH_DT), np.zeros(nr.value, ROT_DT)
+    assert ROT_DT.itemsize == 48
+    assert lib.b200vqe_debug_rotation_runs(*args, vp(B), vp(R)) == 0
+    return B, R
+
+
+def replay_rotation_runs(n, B, R, psi, c=3):
+    """What k_rot_tile does: per run, every tile (coset of the run's subspace) is loaded, the run's rotations are applied to it in
+    order -- pairs {v, v ^ xv} of the virtual index with bit hb of v clear; a' = c a + m s(w) b, b' = c b + m s(v) a; diagonal
+    strings multiply by c + m s(v) -- and the tile is written back."""
+    M = TILE_BITS - c
+    v = np.arange(1 << TILE_BITS, dtype=np.uint64)
+    mu, lo = v >> np.uint64(c), v & np.uint64((1 << c) - 1)
+    psi = psi.copy()
+    for b in B:
+        combo = np.zeros(1 << TILE_BITS, np.uint64)
+        for i in range(M):
+            combo ^= np.where((mu >> np.uint64(i)) & np.uint64(1), np.uint64(b["basis"][i]), np.uint64(0)).astype(np.uint64)
+        for t in range(1 << (n - TILE_BITS)):
+            rep = 0
+            for i in range(11):
+                rep |= (t & int(b["seg"][i])) << i
+            j = (((np.uint64(rep) ^ combo) << np.uint64(c)) | lo).astype(np.int64)
+            assert len(set(j.tolist())) == 1 << TILE_BITS
+            tile = psi[j]
+            for rec in R[b["r_begin"]:b["r_end"]]:
+                xv, zv = int(rec["xv"]), np.uint64(rec["zv"])
+                cpar = bin(rep & int(rec["zl"])).count("1") & 1
+                s = 1.0 - 2.0 * (cpar ^ parity(v & zv))                 # s(v) for every virtual index
+                m = complex(rec["mre"], rec["mim"])
+                if xv == 0:
+                    tile = (rec["c"] + m * s) * tile
+                    continue
+                hb = int(rec["hb"])
+                assert xv >> hb == 1
+                va = v[((v >> np.uint64(hb)) & np.uint64(1)) == 0].astype(np.int64)
+                wa = va ^ xv
+                a, bb = tile[va].copy(), tile[wa].copy()
+                assert np.all(s[wa] == s[va] * (1.0 - 2.0 * int(rec["flip"])))
+                tile[va] = rec["c"] * a + m * s[wa] * bb
+                tile[wa] = rec["c"] * bb + m * s[va] * a
+            psi[j] = tile
+    return psi
+
+
+@pytest.mark.parametrize("n,kind,seed", [(13, "random", 1), (15, "low-weight", 2), (14, "same-support", 3), (16, "uccsd", 4)])
+def test_rotation_runs_replay_matches_oracle(n, kind, seed):
+    """Host logic of the fused ansatz rotations (b200vqe_apply_pauli_rotations -> k_rot_tile) on the CPU: the runs the host cuts
+    a rotation list into -- consecutive rotations whose flip masks span <= 9 high-index dimensions -- replayed in numpy with the
+    kernel's index arithmetic give the oracle's state after the same rotations applied one by one, in order."""
+    rng = np.random.default_rng(seed)
+    if kind == "uccsd":
+        x, z, ic, pa, npar = xb.uccsd_rotations(n, 4, "jw")
+        keep = np.sort(rng.choice(len(x), 120, replace=False))
+        xm, zm, phi = x[keep], z[keep], (ic * rng.uniform(-0.4, 0.4, npar)[pa])[keep]
+    elif kind == "same-support":
+        sup = [int(s) for s in rng.integers(1, 1 << n, 6, dtype=np.uint64)]
+        xm = np.array([sup[i // 8 % 6] for i in range(96)], np.uint64)
+        zm = rng.integers(0, 1 << n, 96, dtype=np.uint64)
+        phi = rng.normal(size=96)
+    else:
+        xm, zm, _ = random_hamiltonian(n, 90, 40 + seed, None if kind == "random" else (0.8, 0.07, 0.06, 0.07))
+        xm = xm.copy()
+        xm[::11] = 0
+        phi = rng.normal(size=len(xm))
+        phi[3] = 0.0
+    B, R = get_rotation_runs(n, xm, zm, phi)
+    assert len(R) == int(np.count_nonzero(phi)) and B["r_end"][-1] == len(R) and B["r_begin"][0] == 0
+    if kind != "random":
+        assert len(B) * 4 <= len(R)                      # structured lists: many rotations per HBM pass
+    psi = rng.normal(size=1 << n) + 1j * rng.normal(size=1 << n)
+    psi /= np.linalg.norm(psi)
+    want = psi.copy()
+    for x, z, p in zip(xm, zm, phi):
+        if p != 0.0:
+            co.pauli_rotation(n, int(x), int(z), float(p), want)
+    got = replay_rotation_runs(n, B, R, psi)
+    assert np.abs(got - want).max() < 1e-12
