@@ -367,8 +367,9 @@ static int create_common(int n_qubits, int device, int rank, int world, const ch
         set((const void *)k_tile_expect_db<3>, two_small);
         set((const void *)k_tile_apply_pipe8<false>, kApply8SmemBytes);
         set((const void *)k_tile_apply_pipe8<true>, kApply8SmemBytes);
-        set((const void *)k_tile_expect_pipe<false>, kPipeSmemBytes);
-        set((const void *)k_tile_expect_pipe<true>, kPipeSmemBytes);
+        set((const void *)k_tile_expect_pipe<0>, kPipeSmemBytes);
+        set((const void *)k_tile_expect_pipe<1>, kPipeSmemBytes);
+        set((const void *)k_tile_expect_pipe<2>, kPipeSmemBytes);
         set((const void *)k_sweep_small, tile);
         set((const void *)k_rot_tile, tile);
         if (ea != cudaSuccess) return fail(std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(ea), B200VQE_ECUDA);

@@ -244,10 +244,12 @@ struct PipeFillBatch {               // what a fill needs of its batch (shared m
 };
 constexpr int kPipeSmemBytes = kRingStages * kRingTileBytes + kRingGroups * (int)(sizeof(RingTables) + sizeof(PipeFillBatch)) + kRingGroups * kRingStages * 8 + 32 * 8;
 
-// WIDE = false: one register of at most 32 qubits (sel_mask = 0): a tile row is addressed by a 32-bit ELEMENT index
+// FILL = 0: one register of at most 32 qubits (sel_mask = 0): a tile row is addressed by a 32-bit ELEMENT index
 // (high index << C | low bits) XORed with one of 16 per-batch row constants -- LOP3 + IMAD.WIDE + LDGSTS per row.
-// WIDE = true: pair registers of a sharded handle and registers above 32 qubits: 64-bit chunk arithmetic per row.
-template <bool WIDE>
+// FILL = 1: pair register of a sharded handle, at most 32 qubits together: the same element index; its top bit picks the slab
+// (this rank's or the one received from the peer), the rest indexes it -- two SELs more per row.
+// FILL = 2: anything larger: 64-bit chunk arithmetic per row.
+template <int FILL>
 __global__ void __launch_bounds__(kRingThreads, 1)
 k_tile_expect_pipe(const double2 *__restrict__ psi, const double2 *__restrict__ psi_hi, unsigned sel_mask, int C, int M,
                    const TileBatch *__restrict__ batches, int n_batches,
@@ -317,7 +319,7 @@ k_tile_expect_pipe(const double2 *__restrict__ psi, const double2 *__restrict__ 
         const unsigned rb0 = fb.basis[M - 4], rb1 = fb.basis[M - 3], rb2 = fb.basis[M - 2], rb3 = fb.basis[M - 1];
         const unsigned base = f_rep ^ f_tc;
         const unsigned dst = tiles_u + (unsigned)fs * kRingTileBytes + (v0 << 4);
-        if constexpr (WIDE) {
+        if constexpr (FILL == 2) {
             const unsigned lm0 = fb.lam[0] << 4, lm1 = fb.lam[1] << 4, lm2 = fb.lam[2] << 4, lm3 = fb.lam[3] << 4;
 #pragma unroll
             for (int r = 0; r < 16; ++r) {
@@ -333,7 +335,12 @@ k_tile_expect_pipe(const double2 *__restrict__ psi, const double2 *__restrict__ 
 #pragma unroll
             for (int r = 0; r < 16; ++r) {
                 const unsigned e = e0 ^ ((r & 1) ? g0 : 0u) ^ ((r & 2) ? g1 : 0u) ^ ((r & 4) ? g2 : 0u) ^ ((r & 8) ? g3 : 0u);
-                cp_async16_u(dst + ((unsigned)r << 12), psi + e);
+                if constexpr (FILL == 0) cp_async16_u(dst + ((unsigned)r << 12), psi + e);
+                else {
+                    // sel_mask is the slab bit of the HIGH index (j >> C): element bit sel_mask << C
+                    const unsigned top = sel_mask << C;
+                    cp_async16_u(dst + ((unsigned)r << 12), ((e & top) ? psi_hi : psi) + (e & (top - 1u)));
+                }
             }
         }
         cp_async_arrive_noinc(full_u + 8 * (kRingGroups * fs + (1 - g)));   // the item is walked by the other group
