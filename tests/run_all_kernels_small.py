@@ -30,10 +30,10 @@ def main():
         be.set_option("tile-bits", tile_bits)
         be.set_hamiltonian(xm, zm, cf)
         be.upload(psi)
-        assert abs(be.expectation() - eo) < 1e-10 * scale                       # k_tile_expect<2> / k_tile_expect_db<3>
+        assert abs(be.expectation() - eo) < 1e-10 * scale                       # k_tile_expect_pipe (views, fused blocks) / k_tile_expect_db<3>
         e, per = be.expectation(per_term=True)                                  # k_tile_expect<2, true> (tile_bits 12)
         assert np.abs(per - pero.real).max() < 1e-11
-        be.apply_h(0, 1)                                                        # k_tile_apply
+        be.apply_h(0, 1)                                                        # k_tile_apply_pipe8
         assert np.abs(be.download(1) - ref).max() < 1e-12 * scale
         be.set_number_sector(n // 2, "bk")                                      # k_project_sector
         be.project_sector(0)
@@ -49,7 +49,7 @@ def main():
     es = be.sweep_energies(0b1111, x, z, ic, pa, npar, th)                      # k_sweep_small
     for v in range(3):
         be.reset(0, 0b1111)
-        be.apply_pauli_rotations(x, z, ic * th[v][pa])                          # k_pauli_rotation
+        be.apply_pauli_rotations(x, z, ic * th[v][pa])                          # k_pauli_rotation (below one tile: no fused runs)
         assert abs(be.expectation().real - es[v]) < 1e-12 * np.abs(cs).sum()
     be.close()
     print("all kernels small: ok")

@@ -249,7 +249,7 @@ def get_apply_plan(n, c, xm, zm, cf, rank=0, world=1):
 
 
 def replay_apply(n, c, B, R, T, classes, psi, rank=0, world=1):
-    """What k_tile_apply computes for shard `rank`: for every x_rank class the partners come from the slab of rank ^ x_rank;
+    """What k_tile_apply_pipe8 computes for shard `rank`: for every x_rank class the partners come from the slab of rank ^ x_rank;
     per record, output v of a tile receives f(v) * src[v ^ xv] (times i for odd nY), f(v) = sum_e u_e (-1)^sign_e(v) with the
     sign evaluated at the thread's OWN index.  Returns the local slab of H psi."""
     nl = n - int(np.log2(world))

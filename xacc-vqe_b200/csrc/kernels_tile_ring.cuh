@@ -85,20 +85,11 @@ struct RingCursor {
 };
 
 // ---------------------------------------------------------------------------------------------
-// The same ring filled with cp.async (LDGSTS, 16 B per thread) instead of bulk copies: k_tile_expect_pipe, the default.
-//
-// Why: cp.async.bulk compiles to UBLKCP, a UNIFORM-datapath instruction -- one copy per warp-instruction, its operands in
-// uniform registers.  A warp whose lanes hold 32 different chunk addresses is serialised by the compiler into an
-// ELECT / 4 x R2UR.BROADCAST / UBLKCP / BRA.U.ANY loop (see the SASS of k_tile_expect_ring): ~9 issue slots per 128-byte
-// chunk, 512 chunks per tile = ~4600 warp-instructions per tile, against 128 LDGSTS warp-instructions (+ addresses) for
-// the same 64 KB.  The cosets of a GF(2) subspace are XOR-scattered 128-byte chunks, so there is no larger contiguous
-// run for a bulk copy and no affine tensor map that describes a tile.
-//
-// Every thread copies exactly the 16 amplitudes it owns, so the tile lands in the SHEARED (thread, register) layout the
-// records are planned for and the walk is the plain code of kernels_tile.cuh (partner rows at immediate offsets).
-// Completion is still an mbarrier per stage: every copying thread issues cp.async.mbarrier.arrive.noinc on full[s].
-// The group that walked item i is the one that refills its stage with item i + 3 (after a barrier of that group only),
-// so no "empty" barrier is needed: group 0 streams the odd items, group 1 the even ones.
+// k_tile_expect_pipe.  Every thread copies exactly the 16 amplitudes it owns in view 0 with cp.async (LDGSTS, 16 B each), so the
+// tile lands in the SHEARED (thread, register) layout the records are planned for; completion is an mbarrier per (stage,
+// walking group): every copying thread issues cp.async.mbarrier.arrive.noinc.  The group that walked item i is the one that
+// refills its stage with item i + 3 (after a barrier of that group only), so no "empty" barrier is needed: group 0 streams
+// the odd items, group 1 the even ones.  (Why not cp.async.bulk: see the header of this file.)
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ void cp_async_arrive_noinc(unsigned bar) {
     asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
