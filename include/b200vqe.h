@@ -242,6 +242,32 @@ int b200vqe_sweep_energies(b200vqe_handle h, uint64_t basis_index, int64_t n_rot
                            const uint64_t *zmask, const double *imag_coeff, const int32_t *param,
                            int n_params, int64_t n_vec, const double *theta, double *energies);
 
+/* ------------------------------------------------------------------ allocation-free entry point
+ * No counterpart in the reference (its vectors are host Eigen/PETSc objects; nothing there has a device allocator to avoid).
+ *
+ * out_re_im[0..1] = <bra|ket> = sum_j conj(bra_j) ket_j of two device vectors the CALLER owns, for hosts that must not
+ * (or cannot) let this library allocate device memory: a simulator that has already filled the HBM with its own
+ * register, a process whose device memory is managed by a single pool allocator, a loop that cannot take the
+ * device-wide stall of cudaMalloc/cudaFree.  It needs no handle and calls no cudaMalloc, cudaFree or other allocating
+ * routine.  The block sums of the reduction live in a static device array inside the library image instead
+ * (B200VQE_NOALLOC_SCRATCH_BYTES on every GPU that loads the library, held until the process exits).
+ *   bra, ket     device pointers on the CURRENT device, 16-byte aligned, n_amplitudes interleaved (re, im) doubles each
+ *   out_re_im    device pointer (8-byte aligned), two doubles; written by the kernel in stream order -- the call does not synchronise
+ *   stream       a cudaStream_t, or NULL for the default stream
+ *   errbuf       nullable; receives the message of a failed call (errbuf_len bytes, NUL-terminated)
+ * Limits: 1 <= n_amplitudes <= B200VQE_NOALLOC_MAX_AMPLITUDES, and a device of at most B200VQE_NOALLOC_MAX_CTAS / 4 SMs
+ * (a B200 has 148); anything larger is refused with B200VQE_EINVAL and a message, never truncated.
+ * The first call on each device looks up the array's address on that device (and may load the library's GPU code):
+ * make that first call outside any stream capture.  All calls on one GPU share the one array: the call clears what has to
+ * start at zero itself, but two calls whose kernels can overlap on the GPU (different streams, or different host threads
+ * without ordering) race on it and return garbage -- order them on one stream or with events.
+ * Same summation order as b200vqe_state_inner on a one-GPU handle of the same length. */
+#define B200VQE_NOALLOC_MAX_AMPLITUDES ((uint64_t)1 << 33)   /* 2^33 amplitudes = 128 GiB per vector */
+#define B200VQE_NOALLOC_MAX_CTAS 1024
+#define B200VQE_NOALLOC_SCRATCH_BYTES 16640                  /* 2 x 1024 block sums + one 256-byte line for the ticket */
+int b200vqe_inner_noalloc(const double *bra, const double *ket, uint64_t n_amplitudes, double *out_re_im, void *stream,
+                          char *errbuf, int64_t errbuf_len);
+
 /* Timing / accounting helpers used by bench.py */
 int b200vqe_synchronize(b200vqe_handle h);
 int b200vqe_kernel_launches(b200vqe_handle h, int64_t *count);    /* kernels launched by this handle so far */

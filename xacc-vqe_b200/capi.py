@@ -65,6 +65,25 @@ def _f64(a):
     return np.ascontiguousarray(a, dtype=np.float64)
 
 
+NOALLOC_MAX_AMPLITUDES = 1 << 33   # B200VQE_NOALLOC_MAX_AMPLITUDES
+
+
+def inner_noalloc(bra_ptr: int, ket_ptr: int, n_amplitudes: int, out_ptr: int, stream: int = 0) -> None:
+    """b200vqe_inner_noalloc: <bra|ket> of two device vectors the caller owns, written to the caller's two device
+    doubles at out_ptr in stream order (no synchronisation, no handle, no device allocation -- for hosts whose HBM is
+    already spoken for or belongs to a pool allocator).  The arguments are raw device addresses (e.g.
+    tensor.data_ptr()) on the current device and a cudaStream_t as an integer.  Calls share one static scratch array
+    per GPU, so keep them ordered on the GPU; see include/b200vqe.h for the limits."""
+    L = lib()
+    L.b200vqe_inner_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int64]
+    L.b200vqe_inner_noalloc.restype = C.c_int
+    err = C.create_string_buffer(512)
+    rc = L.b200vqe_inner_noalloc(C.c_void_p(bra_ptr), C.c_void_p(ket_ptr), C.c_uint64(n_amplitudes), C.c_void_p(out_ptr),
+                                 C.c_void_p(stream), err, C.c_int64(len(err)))
+    if rc:
+        raise B200Error(rc, err.value.decode())
+
+
 # --------------------------------------------------------------------------- front end
 class OpHandle:
     """Owns a b200vqe_op."""
