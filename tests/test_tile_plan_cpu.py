@@ -579,3 +579,20 @@ def test_rotation_runs_replay_matches_oracle(n, kind, seed):
             co.pauli_rotation(n, int(x), int(z), float(p), want)
     got = replay_rotation_runs(n, B, R, psi)
     assert np.abs(got - want).max() < 1e-12
+
+
+@pytest.mark.parametrize("n,ok", [(11, False), (12, True), (32, True), (33, False), (35, False)])
+def test_rotation_run_planner_refuses_registers_beyond_32_bit_indices(n, ok):
+    """k_rot_tile forms 32-bit element indices, so fused runs exist only for 12 <= local qubits <= 32 (a 33-qubit register fits a
+    B200 and must fall back to one k_pauli_rotation launch per rotation).  b200vqe_apply_pauli_rotations and this host-only
+    planner export share the predicate (rot_tile_supports, csrc/backend_state.inc)."""
+    lib = xb.capi.lib()
+    top = np.uint64(1) << np.uint64(n - 1)
+    xm, zm = np.array([top | np.uint64(1), top], np.uint64), np.array([np.uint64(2), top], np.uint64)
+    phi = np.array([0.3, -0.2])
+    nb, nr = C.c_int64(), C.c_int64()
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)
+    rc = lib.b200vqe_debug_rotation_runs(C.c_int(n), C.c_int64(2), vp(xm), vp(zm), vp(phi), C.byref(nb), C.byref(nr), None, None)
+    assert (rc == 0) == ok, rc
+    if ok:
+        assert nb.value >= 1 and nr.value == 2
