@@ -155,17 +155,19 @@ def host_random_state(n: int):
 
 def cpu_baseline(co, n: int, xm, zm, cf, n_sample_terms: int):
     """The oracle (C/OpenMP mask-based port of the reference algorithm) timed on the host cores on a
-    bounded sample: the same register size, the first `n_sample_terms` terms.  Returns (record, seconds, k, energy)."""
+    bounded sample: the same register size, a seeded random subset of `n_sample_terms` terms.  Returns (record, seconds, selected indices, energy)."""
     N = 1 << n
     psi = host_random_state(n)
     k = min(n_sample_terms, len(xm))
+    # a seeded RANDOM subset: the terms arrive sorted by xmask, so the first k would be the k smallest flip masks (top qubits never flipped)
+    sel = np.sort(np.random.default_rng(SEED + 2).choice(len(xm), size=k, replace=False))
     co.expect(n, xm[:1], zm[:1], cf[:1], psi)          # warm up threads / page in
     t0 = time.perf_counter()
-    e, _ = co.expect(n, xm[:k], zm[:k], cf[:k], psi)
+    e, _ = co.expect(n, xm[sel], zm[sel], cf[sel], psi)
     dt = time.perf_counter() - t0
     return ({"value": k * N / dt, "unit": UNIT, "cores": co.num_threads(), "kind": "port",
-             "sample": f"{k} of {len(xm)} terms on the full 2^{n} register, C/OpenMP mask-based oracle (oracle/hpsi_oracle.c), {dt:.2f} s"},
-            dt, k, e)
+             "sample": f"seeded random {k} of {len(xm)} terms on the full 2^{n} register, C/OpenMP mask-based oracle (oracle/hpsi_oracle.c), {dt:.2f} s"},
+            dt, sel, e)
 
 
 def mem_available_bytes() -> int:
@@ -332,12 +334,14 @@ def run_gpu(args):
     cpu_base = None
     if world == 1 and not args.no_cpu:
         co = load_oracle()
-        cpu_base, _, k_cpu, e_cpu = cpu_baseline(co, n, xm, zm, cf, args.cpu_terms)
-        be.set_hamiltonian(xm[:k_cpu], zm[:k_cpu], cf[:k_cpu])
+        cpu_base, _, sel, e_cpu = cpu_baseline(co, n, xm, zm, cf, args.cpu_terms)
+        be.set_hamiltonian(xm[sel], zm[sel], cf[sel])
         be.upload(host_random_state(n))
         e_gpu = be.expectation()
         check["random_state_vs_oracle_rel_err"] = abs(e_gpu - e_cpu) / abs(e_cpu)
-        check["random_state_vs_oracle_terms"] = int(k_cpu)
+        check["random_state_vs_oracle_terms"] = int(len(sel))
+        check["random_state_vs_oracle_plan"] = ("a plan built for the seeded random subset of terms (not the timed plan); the timed plan is exercised by "
+                                                "product_state_rel_err (all terms, exact answer) and expect_vs_apply_rel_err (all terms, random state)")
         check["random_state_energy"] = [e_gpu.real, e_cpu.real]
         if not check["random_state_vs_oracle_rel_err"] <= GUARD_TOL:
             failures.append(f"random-state <psi|H|psi> differs from the oracle by {check['random_state_vs_oracle_rel_err']:.3e} relative")
@@ -380,7 +384,7 @@ def run_gpu(args):
             e = step()
             kernel_ms.append(be.last_kernel_ms())
             if world > 1 and op == "expect":
-                xch.append(be.last_exchange())
+                xch.append(be.last_exchange() + (be.last_exchange_exposed(),))
         ms = be.timer_stop()
         barrier()
     launches = be.kernel_launches() - l0
@@ -422,20 +426,40 @@ def run_gpu(args):
            "value_with_set_hamiltonian_every_step": Tn * N / (dt + set_ham_ms * 1e-3)}
     del host
 
-    # ---- extra: H psi and one Lanczos step on the same operator (N = 1; the headline stays <psi|H|psi>) ----
+    # ---- extra: H psi and one Lanczos step on the same operator at every N (the headline stays <psi|H|psi>) ----
+    # Sharded: times are the max over ranks; the slab exchange of H psi (option shard-exchange, default one ncclAllGather per H psi)
+    # is reported with its CUDA-event transfer time and the time the compute stream waited for it (exposed).
     extra = {}
-    if world == 1 and op == "expect" and not args.no_extra:
+    if op == "expect" and not args.no_extra:
+        def max_over_ranks(v):
+            if world == 1:
+                return float(v)
+            tv = torch.tensor([float(v)], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tv, op=dist.ReduceOp.MAX)
+            return float(tv.item())
+
         be.n_slots(3)
         be.random_state(0, SEED)
-        be.apply_h(0, 1, want_alpha=False)             # plans H psi, warms up
-        be.synchronize()
+        alpha = be.apply_h(0, 1, want_alpha=True)      # plans H psi, warms up; alpha = <psi|H psi> through the H psi engine
+        # (iv) the TIMED <psi|H|psi> plan on a random state, all terms: against <psi|(H psi)> from the independently planned H psi engine
+        e_expect = be.expectation()
+        check["expect_vs_apply_rel_err"] = abs(e_expect.real - alpha.real) / abs(alpha.real)
+        check["expect_vs_apply_energy"] = [e_expect.real, alpha.real]
+        if not check["expect_vs_apply_rel_err"] <= GUARD_TOL:
+            failures.append(f"random-state <psi|H|psi> (timed plan) and <psi|(H psi)> differ by {check['expect_vs_apply_rel_err']:.3e} relative")
+        barrier()
         la = be.kernel_launches()
-        t_ms = []
+        t_ms, x_ms_a, x_by_a, x_exp_a = [], [], [], []
         for _ in range(2):
             be.apply_h(0, 1, want_alpha=False)
             t_ms.append(be.last_kernel_ms())
+            if world > 1:
+                xm_, xb_ = be.last_exchange()
+                x_ms_a.append(xm_)
+                x_by_a.append(xb_)
+                x_exp_a.append(be.last_exchange_exposed())
         la = (be.kernel_launches() - la) // 2
-        a_ms = float(np.mean(t_ms))
+        a_ms = max_over_ranks(np.mean(t_ms))
         nb_a = be.plan_stats()["apply_batches"]
         peak, _ = measured_peak_gbs()
         alg = 16.0 * be.n_local * (G + 1)
@@ -444,9 +468,15 @@ def run_gpu(args):
                           "launches": int(la), "n_batches": int(nb_a),
                           "roofline": {"bound": "hbm", "achieved": alg / (a_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                                        "frac": alg / (a_ms * 1e-3) / 1e9 / peak,
-                                       "note": "ALGORITHMIC bytes 16 B x 2^n x (G + 1) (SURVEY.md 8d) / CUDA-event time",
+                                       "note": "per GPU: ALGORITHMIC bytes 16 B x 2^n_local x (G + 1) (SURVEY.md 8d) / CUDA-event time (max over ranks)",
                                        "dram_model": {"bytes": model, "achieved": model / (a_ms * 1e-3) / 1e9, "frac": model / (a_ms * 1e-3) / 1e9 / peak,
-                                                      "note": "16 B x 2^n x (3 n_batches - 1): src read + dst read + dst write per batch of xmask groups"}}}
+                                                      "note": "16 B x 2^n_local x (3 n_batches - 1): src read + dst read + dst write per batch of xmask groups (rank 0's plan)"}}}
+        if world > 1:
+            xm_ms = float(np.mean(x_ms_a))
+            extra["apply"]["nvlink"] = {"exchange": "nccl (shard-exchange = auto: one ncclAllGather of the register per H psi, or send/recv of the needed slabs)",
+                                        "bytes_per_gpu": float(np.mean(x_by_a)), "exchange_ms": xm_ms, "exposed_ms": float(np.mean(x_exp_a)),
+                                        "achieved": float(np.mean(x_by_a)) / (xm_ms * 1e-3) / 1e9 if xm_ms > 0 else None, "peak": NVLINK_NOMINAL_GBS,
+                                        "unit": "GB/s", "note": "rank 0's figures; exposed_ms = CUDA-event time the compute stream waited for the slabs"}
         # one Lanczos iteration = H psi (alpha fused or one k_alpha pass) + k_lanczos_update; measured as the slope of two short runs
         m1, m2 = 3, 9
 
@@ -458,21 +488,25 @@ def run_gpu(args):
                     raise
             be.synchronize()
 
+        barrier()
         t0 = time.perf_counter()
         lanczos_steps(m1)
+        barrier()
         d1 = time.perf_counter() - t0
         l1 = be.kernel_launches()
         t0 = time.perf_counter()
         lanczos_steps(m2)
+        barrier()
         d2 = time.perf_counter() - t0
         l2 = be.kernel_launches() - l1
-        it_ms = (d2 - d1) / (m2 - m1) * 1e3
+        it_ms = max_over_ranks((d2 - d1) / (m2 - m1) * 1e3)
         alg_l = alg + 80.0 * be.n_local
         extra["lanczos_step"] = {"op": "one Lanczos iteration: H psi + alpha + three-term update with fused norm", "ms": it_ms,
                                  "value": Tn * N / (it_ms * 1e-3), "unit": UNIT, "launches_per_iteration": int(round(l2 / m2)),
                                  "roofline": {"bound": "hbm", "achieved": alg_l / (it_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                                               "frac": alg_l / (it_ms * 1e-3) / 1e9 / peak,
-                                              "note": "ALGORITHMIC bytes of H psi + 5 x 16 B x 2^n for the fused vector update / host-timed slope of two runs"}}
+                                              "note": "per GPU: ALGORITHMIC bytes of H psi + 5 x 16 B x 2^n_local for the fused vector update / host-timed slope of two runs "
+                                                      "(barrier on both sides, max over ranks)"}}
         be.n_slots(1)
 
     if world > 1:
@@ -551,20 +585,25 @@ def run_gpu(args):
         x_ms = float(np.mean([v[0] for v in xch]))
         x_by = float(np.mean([v[1] for v in xch]))
         gbs = x_by / (x_ms * 1e-3) / 1e9 if x_ms > 0 else None
+        mode = be.exchange_mode()
         roof["nvlink"] = {"bytes_per_gpu_per_step": x_by, "exchange_ms_per_step": x_ms, "achieved": gbs,
+                          "exposed_ms_per_step": float(np.mean([v[2] for v in xch])), "exchange": mode,
                           "peak": NVLINK_NOMINAL_GBS, "unit": "GB/s", "frac": gbs / NVLINK_NOMINAL_GBS if gbs else None,
                           "frac_of_measured_770": gbs / NVLINK_MEASURED_GBS if gbs else None,
                           "exchange_share_of_step": x_ms / k_ms if k_ms > 0 else None,
-                          "note": "slab swaps of the x_rank classes (grouped ncclSend/ncclRecv, both directions at once): bytes this rank RECEIVES per step / "
-                                  "CUDA-event time of the swaps on the communication stream, summed over the classes; the swaps run concurrently with the "
-                                  "tile kernels of the previous class, so exchange_share_of_step is overlapped time, not added time"}
+                          "note": "slab swaps of the x_rank classes (" + ("peer-memory pushes through CUDA IPC staging, copy engine over NVLink, ordered by flag words"
+                                                                               if mode == "peer-copy" else "grouped ncclSend/ncclRecv") +
+                                  ", both directions at once): bytes this rank RECEIVES per step / CUDA-event time of the swaps on the communication stream, "
+                                  "summed over the classes (rank 0's figures).  The swaps run concurrently with the tile kernels of the previous class: "
+                                  "exchange_share_of_step is overlapped time; exposed_ms_per_step is the CUDA-event time the compute stream spent "
+                                  "waiting for a slab (b200vqe_last_exchange_exposed), the part that was not hidden"}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
             "config": {"workload": f"synthetic {n}-qubit random Pauli sum, {Tn} terms, fp64 " + ("H.psi" if apply_op else ("<psi|H|psi> + per-term <P_k>" if op == "terms" else "<psi|H|psi>")),
                        "n_qubits": n, "n_terms": int(Tn), "n_xmask_groups": int(G), "amplitudes_per_gpu": int(be.n_local),
                        "parallelism": f"state sharded over {world} GPU(s) by high index bits" + (
-                           "; per x_rank class the two ranks of a pair swap slabs (ncclSend/ncclRecv) and evaluate half of the pair register each, "
+                           "; per x_rank class the two ranks of a pair swap slabs (" + be.exchange_mode() + ") and evaluate half of the pair register each, "
                            "one ncclAllReduce of the partials" if world > 1 else ""),
                        "l2": "inputs larger than L2 (4.3 GB state per GPU vs 126 MB)"},
             "roofline": roof, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "check": check, "plan": plan}

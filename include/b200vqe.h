@@ -139,6 +139,9 @@ int b200vqe_plan_costs(b200vqe_handle h, int64_t out[4]);
 int b200vqe_last_exchange(b200vqe_handle h, double *ms, double *bytes);
 /* ... and the time [ms] the compute stream WAITED for those transfers (what the kernels queued before each wait did not hide). */
 int b200vqe_last_exchange_exposed(b200vqe_handle h, double *ms);
+/* ... and which transport the slab swaps of the sharded <psi|H|psi> use on this handle: 1 peer-memory copies (CUDA IPC + copy engine),
+ * -1 grouped ncclSend/ncclRecv, 0 not decided yet (decided collectively at the first sharded <psi|H|psi>; always 0 on one GPU). */
+int b200vqe_exchange_mode(b200vqe_handle h, int *mode);
 
 /* Host-only view of the tile-engine plan (see csrc/tile_plan.hpp) for a Hermitian term list, exactly as
  * b200vqe_set_hamiltonian builds it for <psi|H|psi> (batch capacities included): raw TileBatch[160 B],
@@ -183,8 +186,11 @@ int b200vqe_debug_shard_layout(int n_qubits, int rank, int world, int tile_bits,
 int b200vqe_state_reset(b200vqe_handle h, int slot, uint64_t basis_index);
 int b200vqe_state_upload(b200vqe_handle h, int slot, const double *amps, uint64_t first, uint64_t count);
 int b200vqe_state_download(b200vqe_handle h, int slot, double *amps, uint64_t first, uint64_t count, int order);
-        /* order = B200VQE_ORDER_REFERENCE: whole local range only; on a sharded handle the call is collective and rank r
-         * receives the reference indices [r 2^nl, (r + 1) 2^nl) (the register is gathered once: `world` staging slabs) */
+        /* order = B200VQE_ORDER_REFERENCE: whole local range only; on a sharded handle the call is COLLECTIVE (every rank must make it,
+         * or the others wait in the gather for ever) and rank r receives the reference indices [r 2^nl, (r + 1) 2^nl).  It gathers
+         * the whole register on every GPU: 16 B x 2^n for the staging slabs + 16 B x 2^nl for the extraction, i.e. O(2^n) per GPU,
+         * not O(2^n / world) -- 72 GiB at 32 qubits on 8 GPUs.  The ranks check the room together first: B200VQE_ENOMEM on all of
+         * them if any is short.  Registers that only fit sharded: download in device order and permute on the host. */
 int b200vqe_state_random(b200vqe_handle h, int slot, uint64_t seed);            /* normalised complex Gaussian */
 int b200vqe_state_product(b200vqe_handle h, int slot, const double *a, const double *b);
                         /* (x)_q (cos a_q |0> + e^{i b_q} sin a_q |1>) */

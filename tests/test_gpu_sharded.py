@@ -102,7 +102,7 @@ def test_shards_match_oracle(n, T, seed, engine, lanczos, world):
         assert np.linalg.norm(hv - res[0][7] * vec) < 1e-6 * scale
         import pauli_oracle as po
         want, _ = po.ground_state_eigsh(xm, zm, cf, n, tol=1e-13, apply=lambda v: co.apply(n, xm, zm, cf, v))
-        assert abs(res[0][7] - want) < 1e-10 * max(1.0, abs(want))
+        assert abs(res[0][7] - want) < 1e-10 * abs(want)          # truly relative
 
 
 def _gate_program(n, seed):

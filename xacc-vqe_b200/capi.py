@@ -298,6 +298,12 @@ class Backend:
         self._ck(lib().b200vqe_last_exchange_exposed(self.h, C.byref(ms)))
         return ms.value
 
+    def exchange_mode(self) -> str:
+        """Transport of the slab swaps of the sharded <psi|H|psi>: 'peer-copy' | 'nccl' | 'undecided' (b200vqe_exchange_mode)."""
+        m = C.c_int()
+        self._ck(lib().b200vqe_exchange_mode(self.h, C.byref(m)))
+        return {1: "peer-copy", -1: "nccl"}.get(m.value, "undecided")
+
     def reset(self, slot: int = 0, basis_index: int = 0):
         self._ck(lib().b200vqe_state_reset(self.h, C.c_int(slot), C.c_uint64(basis_index)))
 

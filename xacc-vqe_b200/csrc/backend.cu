@@ -252,8 +252,12 @@ static int ensure_peer_staging(b200vqe_ctx *h) {
     h->peer_state = -1;
     const size_t slab = h->nloc * sizeof(double2), bytes = 2 * slab + 4096;
     bool ok = h->opt_peer_copy != 0 && g_cu.load();
-    if (ok && !h->h_seq && cudaMallocHost(&h->h_seq, 1024 * sizeof(unsigned)) != cudaSuccess) { cudaGetLastError(); ok = false; }
+    if (ok && !h->h_seq && cudaMallocHost(&h->h_seq, kFlagRing * sizeof(unsigned)) != cudaSuccess) { cudaGetLastError(); ok = false; }
     void *block = nullptr;
+    struct BlockGuard {          // a CK / NK below returns early: the staging block must not outlive a failed set-up
+        void *&p;
+        ~BlockGuard() { if (p) cudaFree(p); }
+    } block_guard{block};
     cudaIpcMemHandle_t mine{};
     if (ok && cudaMalloc(&block, bytes) != cudaSuccess) { cudaGetLastError(); ok = false; block = nullptr; }
     if (ok && cudaMemsetAsync(static_cast<char *>(block) + 2 * slab, 0, 4096, h->stream) != cudaSuccess) ok = false;
@@ -290,11 +294,11 @@ static int ensure_peer_staging(b200vqe_ctx *h) {
         h->pbuf = static_cast<double2 *>(block);
         h->pflags = reinterpret_cast<unsigned *>(static_cast<char *>(block) + 2 * slab);
         h->peer_state = 1;
+        block = nullptr;         // owned by the handle from here on (b200vqe_destroy frees h->pbuf)
         return 0;
     }
     for (int p = 0; p < h->world; ++p) if (h->peer_pbuf[p]) { cudaIpcCloseMemHandle(h->peer_pbuf[p]); h->peer_pbuf[p] = nullptr; h->peer_pflags[p] = nullptr; }
-    if (block) cudaFree(block);
-    return 0;
+    return 0;                    // block_guard frees the block
 }
 
 // stream `st` waits until the LOCAL flag word has reached `value` (wrap-safe >=); no SM involved
@@ -305,7 +309,12 @@ static int flag_wait(b200vqe_ctx *h, cudaStream_t st, const unsigned *flag, unsi
 }
 // stream `st` sets a flag word in a PEER's memory: a 4-byte copy from a pinned ring (copy engine, no SM)
 static int flag_push(b200vqe_ctx *h, cudaStream_t st, unsigned *remote_flag, unsigned value) {
-    unsigned *src = h->h_seq + (h->h_seq_pos++ & 1023u);
+    // A ring slot is read by its 4-byte copy some time after this function returns, so it may be reused only once that copy is
+    // known to be done: the caller resets h_seq_live after the synchronisation that ends its call (every sharded
+    // b200vqe_expectation does).  (P - 1) (P + 1) pushes per call at world P = 63 at 8.
+    if (h->h_seq_live >= kFlagRing) FAIL(B200VQE_ECOMM, "more than " + std::to_string(kFlagRing) + " flag pushes queued without a synchronisation");
+    ++h->h_seq_live;
+    unsigned *src = h->h_seq + (h->h_seq_pos++ % kFlagRing);
     *src = value;
     CK(cudaMemcpyAsync(remote_flag, src, sizeof(unsigned), cudaMemcpyDefault, st));
     return 0;
@@ -481,10 +490,9 @@ int b200vqe_set_option(b200vqe_handle h, const char *key, const char *value) {
         return 0;
     }
     if (k == "peer-copy") {
-        if (v == "on" || v == "1") h->opt_peer_copy = 1;
-        else if (v == "off" || v == "0") h->opt_peer_copy = 0;
-        else FAIL(B200VQE_EINVAL, "peer-copy must be on or off");
-        if (h->peer_state != 0) FAIL(B200VQE_EINVAL, "peer-copy must be set before the first sharded <psi|H|psi>");
+        if (v != "on" && v != "1" && v != "off" && v != "0") FAIL(B200VQE_EINVAL, "peer-copy must be on or off");
+        if (h->peer_state != 0) FAIL(B200VQE_EINVAL, "peer-copy must be set before the first sharded <psi|H|psi>");   // option left as it was
+        h->opt_peer_copy = (v == "on" || v == "1") ? 1 : 0;
         return 0;
     }
     if (k == "fuse-rotations") {

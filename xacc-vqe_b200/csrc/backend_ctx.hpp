@@ -12,6 +12,7 @@
 
 namespace b200vqe {
 
+constexpr unsigned kFlagRing = 1024;  // pinned ring of flag values (sources of the 4-byte peer flag copies)
 constexpr int kOutDoubles = 256;   // device/host scalar scratch (bucket energies, norms, ...)
 
 struct Bucket { int h; int g_begin; int g_end; };   // h = -1: all-j form (weight 1), else pair form (weight 2)
@@ -103,7 +104,7 @@ struct b200vqe_ctx {
     // words (cuStreamWaitValue32): nothing here needs an SM -- the persistent tile kernels hold every register of every SM, so NCCL's
     // send/recv kernels (and any flag kernel) only run when a tile kernel ends.
     double2 *pbuf = nullptr; unsigned *pflags = nullptr;              // flags: [0,1] arrived[b]; [4 + 2 p + b] free_from[p][b]: peer p is done with ITS buffer b
-    unsigned *h_seq = nullptr; unsigned h_seq_pos = 0;                 // pinned ring of sequence numbers: sources of the 4-byte flag copies
+    unsigned *h_seq = nullptr; unsigned h_seq_pos = 0, h_seq_live = 0;                 // pinned ring of sequence numbers: sources of the 4-byte flag copies
     double2 *peer_pbuf[b200vqe::kMaxWorld] = {}; unsigned *peer_pflags[b200vqe::kMaxWorld] = {};
     int peer_state = 0;                                                // 0 not tried, 1 ready, -1 unavailable (NCCL send/recv instead)
     unsigned xseq = 0, buf_last_seq[2] = {0, 0};                       // exchange sequence numbers (identical on every rank)
