@@ -15,9 +15,13 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def test_library_exports_every_declared_symbol():
-    hdr = open(os.path.join(ROOT, "include", "b200vqe.h")).read()
-    names = sorted(set(re.findall(r"\b(b200vqe_[a-z0-9_]+)\s*\(", hdr)))
+    import glob
+    headers = sorted(glob.glob(os.path.join(ROOT, "include", "*.h")))
+    assert [os.path.basename(h) for h in headers] == ["b200vqe.h", "b200vqe_debug.h"]
+    names = sorted({n for h in headers for n in re.findall(r"\b(b200vqe_[a-z0-9_]+)\s*\(", open(h).read())})
     assert len(names) >= 35
+    # the drop-in ABI header carries no planner/debug exports
+    assert "b200vqe_debug_" not in re.sub(r"/\*.*?\*/", "", open(headers[0]).read(), flags=re.S)
     lib = xb.capi.lib()
     missing = [n for n in names if not hasattr(lib, n)]
     assert not missing, missing
@@ -135,6 +139,10 @@ def test_header_is_plain_c_and_example_links(tmp_path):
     subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", os.path.join(ROOT, "include"),
                            os.path.join(ROOT, "examples", "h2_ground_state.c"), "-L", lib_dir, "-lb200vqe",
                            "-Wl,-rpath," + lib_dir, "-o", exe])
+    probe = tmp_path / "dbg.c"          # the debug header is plain C as well
+    probe.write_text('#include "b200vqe_debug.h"\nint main(void) { return b200vqe_debug_set_planner(3); }\n')
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", os.path.join(ROOT, "include"), str(probe),
+                           "-L", lib_dir, "-lb200vqe", "-Wl,-rpath," + lib_dir, "-o", str(tmp_path / "dbg")])
     r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
     assert "H2: 4 qubits, 15 Pauli terms" in r.stdout
     if _has_gpu():

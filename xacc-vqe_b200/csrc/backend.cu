@@ -1,5 +1,6 @@
 // Device backend behind the C ABI of include/b200vqe.h.  One context = one GPU (one shard).
 #include "../../include/b200vqe.h"
+#include "../../include/b200vqe_debug.h"
 #include "backend_ctx.hpp"
 #include "kernels_apply.cuh"
 #include "kernels_small.cuh"
