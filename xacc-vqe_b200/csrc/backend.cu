@@ -17,6 +17,7 @@
 #include <new>
 #include <stdexcept>
 #include <dlfcn.h>
+#include <nvtx3/nvToolsExt.h>   // header-only: ranges cost nothing unless a profiler injects itself (tracing)
 #include <numeric>
 
 using namespace b200vqe;
@@ -119,6 +120,15 @@ static int guarded(b200vqe_ctx *h, F &&body) noexcept {
         return B200VQE_EINVAL;
     }
 }
+// NVTX range around the hot entry points (set_hamiltonian, expectation, apply_h, lanczos_ground, the ansatz calls, sweep_energies): the
+// counterpart of the reference's per-task timing prints; visible in nsys / ncu --nvtx, a no-op otherwise.
+struct NvtxRange {
+    explicit NvtxRange(const char *name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+    NvtxRange(const NvtxRange &) = delete;
+    NvtxRange &operator=(const NvtxRange &) = delete;
+};
+
 #define LAUNCHED(h) do { ++(h)->launches; CK(cudaGetLastError()); } while (0)
 
 // A public call that writes slot 1 or 2 destroys the two live vectors of an unfinished Lanczos run kept for resume / checkpoint.
